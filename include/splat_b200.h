@@ -1,0 +1,144 @@
+/*
+ * splat_b200.h — C-ABI of the B200-native (sm_100a) surfel spherical rasterizer and
+ * distCUDA2 kNN scale initialiser.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch / C++ types.
+ * Every DEVICE pointer must live on the device that is current when the call is
+ * made; every kernel is launched on the `stream` passed in (a cudaStream_t cast to
+ * void*; NULL = legacy default stream, where the reference launches everything).
+ *
+ * Each entry point cites the reference interface it replaces (paths relative to the
+ * reference repo, DSSR = submodules/diff-surfel-spherical-rasterization,
+ * SKNN = submodules/simple-knn).
+ *
+ * Return value: 0 on success, non-zero on error; the message is available from
+ * splat_last_error() (thread-local).  The Python binding turns that into
+ * RuntimeError, like TORCH_CHECK / CHECK_CUDA do in the reference
+ * (DSSR/rasterize_points.cu:21-22, DSSR/cuda_rasterizer/auxiliary.h:368-377).
+ */
+#ifndef SPLAT_B200_H_
+#define SPLAT_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define SPLAT_API __attribute__((visibility("default")))
+#else
+#define SPLAT_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Growable-buffer callback: returns a DEVICE pointer to at least `bytes` bytes that
+ * stays valid until the matching backward has run.  Mirrors
+ * std::function<char*(size_t)> (DSSR/cuda_rasterizer/rasterizer.h:10-12) and the
+ * resize lambdas of DSSR/rasterize_points.cu:24-30. */
+typedef char *(*splat_alloc_fn)(void *ctx, size_t bytes);
+
+/* ---- rasterizer forward --------------------------------------------------------
+ * Replaces CudaRasterizer::Rasterizer::forward
+ * (DSSR/cuda_rasterizer/rasterizer.h:12-21, rasterizer_impl.cu:170-262) as called
+ * by RasterizeGaussiansCUDA (DSSR/rasterize_points.cu:32-88). */
+typedef struct {
+  int P, W, H;                   /* surfels, image width, image height             */
+  float scale_modifier;
+  int prefiltered;               /* as reference: a culled surfel is then an error */
+  int debug;                     /* bit0: synchronise + check after every launch
+                                    (CHECK_CUDA); bit1: keep a copy of the unsorted
+                                    keys for dssr_debug_state                      */
+  const float *means3D;          /* [P,3]                                          */
+  const float *opacities;        /* [P]                                            */
+  const float *scales;           /* [P,2] or NULL when transMat_precomp is given   */
+  const float *rotations;        /* [P,4] (w,x,y,z) or NULL                        */
+  const float *transMat_precomp; /* [P,12] or NULL                                 */
+  const float *viewmatrix;       /* [16] device, column-major world->sensor        */
+  const float *projmatrix;       /* [16] device; fx=[0] fy=[5] cx=[8] cy=[9]       */
+  float *out_maps;               /* [7,H,W] written in full                        */
+  int *radii;                    /* [P] written in full                            */
+  splat_alloc_fn geom_alloc;   void *geom_ctx;
+  splat_alloc_fn binning_alloc; void *binning_ctx;
+  splat_alloc_fn image_alloc;  void *image_ctx;
+  /* Optional: instance capacity to pre-allocate for the binning buffer (0 = size it
+   * exactly after the instance count is known, like the reference).  When the hint
+   * is large enough the whole frame is enqueued before the host waits for the
+   * count, so the GPU never idles on the host. */
+  int64_t binning_hint;
+  void *stream;
+} dssr_forward_args;
+
+/* *num_rendered receives the number of (surfel, tile) instances, the value the
+ * reference returns (rasterizer_impl.cu:261). */
+SPLAT_API int dssr_forward(const dssr_forward_args *args, int *num_rendered);
+
+/* ---- rasterizer backward -------------------------------------------------------
+ * Replaces CudaRasterizer::Rasterizer::backward
+ * (DSSR/cuda_rasterizer/rasterizer.h:23-31, rasterizer_impl.cu:266-313) as called
+ * by RasterizeGaussiansBackwardCUDA (DSSR/rasterize_points.cu:90-147).  All seven
+ * gradient arrays are written in full (zeros where the reference leaves its
+ * torch::zeros untouched). */
+typedef struct {
+  int P, W, H, R;                /* R = num_rendered of the forward                */
+  float scale_modifier;
+  int debug;
+  const float *means3D, *scales, *rotations, *transMat_precomp;
+  const float *viewmatrix, *projmatrix;
+  const int *radii;              /* [P] from the forward                           */
+  const char *geom_buffer, *binning_buffer, *image_buffer; /* from the forward     */
+  const float *dL_dout;          /* [7,H,W]                                        */
+  float *dL_dmeans2D;            /* [P,3] (always zero, as in the reference)       */
+  float *dL_dnormal;             /* [P,3] scratch / output                         */
+  float *dL_dopacity;            /* [P]                                            */
+  float *dL_dmeans3D;            /* [P,3]                                          */
+  float *dL_dtransMat;           /* [P,12]                                         */
+  float *dL_dscales;             /* [P,2]                                          */
+  float *dL_drotations;          /* [P,4]                                          */
+  void *stream;
+} dssr_backward_args;
+
+SPLAT_API int dssr_backward(const dssr_backward_args *args);
+
+/* Replaces CudaRasterizer::Rasterizer::markVisible
+ * (DSSR/cuda_rasterizer/rasterizer_impl.cu:117-122, checkFrustum :48-58). */
+SPLAT_API int dssr_mark_visible(int P, const float *means3D, const float *viewmatrix,
+                      const float *projmatrix, unsigned char *present,
+                      void *stream);
+
+/* Buffer sizes the callbacks will be asked for (mirrors required<T>(),
+ * DSSR/cuda_rasterizer/rasterizer_impl.h:59-64). */
+SPLAT_API size_t dssr_geometry_bytes(int P);
+SPLAT_API size_t dssr_image_bytes(int W, int H);
+SPLAT_API size_t dssr_binning_bytes(int64_t capacity, int W, int H, int P, int keep_unsorted);
+
+/* Debug accessor for parity tests: device pointer + element count of an internal
+ * array of the LAST forward that used these buffers.  Names: "depths" f32[P],
+ * "means2D" f32[2P], "transMat" f32[12P] (Tu.xyz0 Tv.xyz0 Tw.xyz1),
+ * "normal_opacity" f32[4P], "tiles_touched" u32[P], "point_offsets" u32[P],
+ * "keys_unsorted" u64[R] (debug bit1), "keys" u64[R], "point_list" u32[R],
+ * "ranges" u32[2*tiles], "final_T" f32[3HW], "n_contrib" u32[2HW].
+ * The reference has no such call; its tests re-derive the same arrays with
+ * GeometryState/BinningState/ImageState::fromChunk (rasterizer_impl.h:18-56).
+ * "transMat" and "normal_opacity" are materialised into `scratch` (device, at least
+ * 16*P floats) because the product stores them in a packed record. */
+SPLAT_API int dssr_debug_state(const char *geom_buffer, const char *binning_buffer,
+                     const char *image_buffer, const char *name, float *scratch,
+                     void **ptr, size_t *count, void *stream);
+
+/* ---- distCUDA2 -----------------------------------------------------------------
+ * Replaces SimpleKNN::knn (SKNN/simple_knn.cu:186-222) as called by distCUDA2
+ * (SKNN/spatial.cu:15-26): mean of the squared distances to the 3 nearest
+ * neighbours of every point.  `workspace` is caller-owned device scratch of at
+ * least sknn_workspace_bytes(P) bytes. */
+SPLAT_API size_t sknn_workspace_bytes(int P);
+SPLAT_API int sknn_dist2(int P, const float *points, float *mean_dists, void *workspace,
+               size_t workspace_bytes, void *stream);
+
+SPLAT_API const char *splat_last_error(void);
+SPLAT_API int splat_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPLAT_B200_H_ */

@@ -1,0 +1,293 @@
+// common.cuh — shared declarations for the sm_100a surfel rasterizer kernels.
+//
+// Buffer layouts (all carved out of the three caller-allocated byte buffers that the
+// reference calls geomBuffer / binningBuffer / imgBuffer,
+// DSSR/cuda_rasterizer/rasterizer_impl.h:18-56 — our internal layout is our own):
+//
+//  geometry buffer  [GeomHeader | rec float4[4P] | cull float4[P] | depths f32[P] |
+//                    xy float2[P] | tiles_touched u32[P] | point_offsets u32[P] |
+//                    chunk_sums u32[nchunk] | chunk_base u32[nchunk]]
+//    rec (64 B / surfel, the only thing the compositing kernels gather):
+//        f4[0] = Tu.x Tu.y Tu.z Tv.x     f4[1] = Tv.y Tv.z Tw.x Tw.y
+//        f4[2] = Tw.z n.x  n.y  n.z      f4[3] = opacity cx cy |Tw|
+//    cull (16 B / surfel): conservative pixel-space box {xmin,xmax,ymin,ymax} outside
+//        of which the surfel provably fails the alpha >= 1/255 test.
+//  image buffer     [final_T f32[3HW] (T, M1, M2) | n_contrib u32[2HW] | ranges uint2[tiles]]
+//  binning buffer   [BinHeader | point_list u32[C] | keys u64[C] | words_a u64[C] |
+//                    words_b u64[C] | (keys_unsorted u64[C]) | sort tables]
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cuda_runtime.h>
+
+#define SPLAT_TILE 16             // BLOCK_X = BLOCK_Y = 16 (DSSR auxiliary.h:19-20)
+#define SPLAT_NEAR 0.1f           // near_n  (auxiliary.h:37)
+#define SPLAT_FAR 120.0f          // far_n   (auxiliary.h:38)
+#define SPLAT_DEPTH_BASE 0x3DCCCCCDu  // float bits of 0.1f; visible depths are > this
+#define SPLAT_DEPTH_BITS 27       // bits(120.0f) - bits(0.1f) < 2^27
+#define SPLAT_ALPHA_MIN 0x3B808081u   // smallest float that is >= 1/255
+
+#define PRE_CHUNK 256             // surfels per preprocess block (one thread each)
+
+#define SORT_THREADS 256
+#define SORT_ITEMS 16                                  // keys per thread per pass
+#define SORT_BLOCK_ELEMS (SORT_THREADS * SORT_ITEMS)   // 4096
+#define SORT_MAX_BINS 1024
+#define SORT_MAX_PASSES 6
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+struct GeomHeader {
+  uint32_t magic;
+  int P, W, H;
+  uint32_t num_rendered;   // written by the chunk-scan kernel
+  uint32_t status;         // bit0: prefiltered violation
+  uint32_t pad[2];
+};
+
+struct GeomLayout {
+  size_t rec, cull, depths, xy, tiles, offsets, chunk_sums, chunk_base, total;
+  int nchunk;
+  __host__ explicit GeomLayout(int P) {
+    nchunk = (P + PRE_CHUNK - 1) / PRE_CHUNK;
+    size_t o = align_up(sizeof(GeomHeader), 256);
+    rec = o;        o = align_up(o + (size_t)P * 64, 256);
+    cull = o;       o = align_up(o + (size_t)P * 16, 256);
+    depths = o;     o = align_up(o + (size_t)P * 4, 256);
+    xy = o;         o = align_up(o + (size_t)P * 8, 256);
+    tiles = o;      o = align_up(o + (size_t)P * 4, 256);
+    offsets = o;    o = align_up(o + (size_t)P * 4, 256);
+    chunk_sums = o; o = align_up(o + (size_t)nchunk * 4, 256);
+    chunk_base = o; o = align_up(o + (size_t)nchunk * 4, 256);
+    total = o + 256;  // slack for aligning the caller's pointer
+  }
+};
+
+struct ImageLayout {
+  size_t final_T, n_contrib, ranges, total;
+  int tiles_x, tiles_y, tiles;
+  __host__ ImageLayout(int W, int H) {
+    tiles_x = (W + SPLAT_TILE - 1) / SPLAT_TILE;
+    tiles_y = (H + SPLAT_TILE - 1) / SPLAT_TILE;
+    tiles = tiles_x * tiles_y;
+    size_t HW = (size_t)W * H;
+    size_t o = 0;
+    final_T = o;   o = align_up(o + HW * 12, 256);
+    n_contrib = o; o = align_up(o + HW * 8, 256);
+    ranges = o;    o = align_up(o + (size_t)tiles * 8, 256);
+    total = o + 256;
+  }
+};
+
+struct SortPlan {
+  int idx_bits, tile_bits, npass;
+  int shift[SORT_MAX_PASSES], bits[SORT_MAX_PASSES];
+  bool ok;
+  __host__ SortPlan(int P, int tiles) {
+    idx_bits = 1;
+    while ((1ll << idx_bits) < (long long)P) idx_bits++;
+    tile_bits = 1;
+    while ((1 << tile_bits) < tiles) tile_bits++;
+    ok = idx_bits + SPLAT_DEPTH_BITS + tile_bits <= 64;
+    npass = 0;
+    for (int i = 0; i < 3; i++) {  // 27 depth bits = 3 x 9
+      shift[npass] = idx_bits + 9 * i;
+      bits[npass] = 9;
+      npass++;
+    }
+    int tb = tile_bits, sh = idx_bits + SPLAT_DEPTH_BITS;
+    int ntp = (tb + 9) / 10;
+    for (int i = 0; i < ntp; i++) {
+      int b = (tb + (ntp - i) - 1) / (ntp - i);  // spread evenly, <= 10
+      shift[npass] = sh;
+      bits[npass] = b;
+      sh += b;
+      tb -= b;
+      npass++;
+    }
+    if (npass > SORT_MAX_PASSES) ok = false;
+  }
+};
+
+struct BinHeader {
+  uint32_t magic;
+  uint32_t capacity;
+  uint32_t keep_unsorted;
+  uint32_t pad[5];
+};
+
+struct BinLayout {
+  size_t words_a, words_b, keys, point_list, keys_unsorted, hist, digit_base, status,
+      tickets, total;
+  size_t status_bytes, hist_bytes;
+  size_t status_off[SORT_MAX_PASSES];  // element offset of each pass in `status`
+  int nblk;
+  __host__ BinLayout(size_t C, int keep_unsorted, const SortPlan &sp) {
+    nblk = (int)((C + SORT_BLOCK_ELEMS - 1) / SORT_BLOCK_ELEMS);
+    if (nblk < 1) nblk = 1;
+    size_t o = align_up(sizeof(BinHeader), 256);
+    // point_list first: its offset must not depend on the capacity, the backward
+    // only knows num_rendered
+    point_list = o; o = align_up(o + C * 4, 256);
+    keys = o;       o = align_up(o + C * 8, 256);
+    words_a = o;    o = align_up(o + C * 8, 256);
+    words_b = o;    o = align_up(o + C * 8, 256);
+    keys_unsorted = o;
+    if (keep_unsorted) o = align_up(o + C * 8, 256);
+    // [hist | tickets | status] are zeroed with ONE memset per forward
+    hist = o;
+    hist_bytes = (size_t)SORT_MAX_PASSES * SORT_MAX_BINS * 4;
+    o = align_up(o + hist_bytes, 256);
+    tickets = o;    o = align_up(o + SORT_MAX_PASSES * 4, 256);
+    status = o;
+    size_t ent = 0;
+    for (int p = 0; p < SORT_MAX_PASSES; p++) {
+      status_off[p] = ent;
+      if (p < sp.npass) ent += (size_t)nblk << sp.bits[p];
+    }
+    status_bytes = ent * 4;
+    o = align_up(o + status_bytes, 256);
+    digit_base = o; o = align_up(o + (size_t)SORT_MAX_PASSES * SORT_MAX_BINS * 4, 256);
+    total = o + 256;
+  }
+};
+
+static inline char *align_ptr(const char *p) {
+  return (char *)(((uintptr_t)p + 255) & ~(uintptr_t)255);
+}
+
+// Kernel-side views ---------------------------------------------------------------
+struct GeomView {
+  GeomHeader *hdr;
+  float4 *rec;
+  float4 *cull;
+  float *depths;
+  float2 *xy;
+  uint32_t *tiles;
+  uint32_t *offsets;
+  uint32_t *chunk_sums;
+  uint32_t *chunk_base;
+  int nchunk;
+};
+struct ImageView {
+  float *final_T;
+  uint32_t *n_contrib;
+  uint2 *ranges;
+  int tiles_x, tiles_y, tiles;
+};
+struct BinView {
+  BinHeader *hdr;
+  unsigned long long *words_a, *words_b, *keys, *keys_unsorted;
+  uint32_t *point_list;
+  uint32_t *hist, *digit_base, *status, *tickets;
+  size_t status_off[SORT_MAX_PASSES];
+  size_t zero_bytes;  // [hist .. end of status) is one contiguous region to clear
+  int nblk;
+};
+
+static inline GeomView make_geom_view(const char *buf, int P) {
+  GeomLayout L(P);
+  char *b = align_ptr(buf);
+  GeomView v;
+  v.hdr = (GeomHeader *)b;
+  v.rec = (float4 *)(b + L.rec);
+  v.cull = (float4 *)(b + L.cull);
+  v.depths = (float *)(b + L.depths);
+  v.xy = (float2 *)(b + L.xy);
+  v.tiles = (uint32_t *)(b + L.tiles);
+  v.offsets = (uint32_t *)(b + L.offsets);
+  v.chunk_sums = (uint32_t *)(b + L.chunk_sums);
+  v.chunk_base = (uint32_t *)(b + L.chunk_base);
+  v.nchunk = L.nchunk;
+  return v;
+}
+static inline ImageView make_image_view(const char *buf, int W, int H) {
+  ImageLayout L(W, H);
+  char *b = align_ptr(buf);
+  ImageView v;
+  v.final_T = (float *)(b + L.final_T);
+  v.n_contrib = (uint32_t *)(b + L.n_contrib);
+  v.ranges = (uint2 *)(b + L.ranges);
+  v.tiles_x = L.tiles_x;
+  v.tiles_y = L.tiles_y;
+  v.tiles = L.tiles;
+  return v;
+}
+static inline BinView make_bin_view(const char *buf, size_t C, int keep_unsorted,
+                                    const SortPlan &sp) {
+  BinLayout L(C, keep_unsorted, sp);
+  char *b = align_ptr(buf);
+  BinView v;
+  v.hdr = (BinHeader *)b;
+  v.words_a = (unsigned long long *)(b + L.words_a);
+  v.words_b = (unsigned long long *)(b + L.words_b);
+  v.keys = (unsigned long long *)(b + L.keys);
+  v.keys_unsorted = keep_unsorted ? (unsigned long long *)(b + L.keys_unsorted) : nullptr;
+  v.point_list = (uint32_t *)(b + L.point_list);
+  v.hist = (uint32_t *)(b + L.hist);
+  v.digit_base = (uint32_t *)(b + L.digit_base);
+  v.status = (uint32_t *)(b + L.status);
+  v.tickets = (uint32_t *)(b + L.tickets);
+  for (int p = 0; p < SORT_MAX_PASSES; p++) v.status_off[p] = L.status_off[p];
+  v.zero_bytes = L.status + L.status_bytes - L.hist;
+  v.nblk = L.nblk;
+  return v;
+}
+
+// records the message returned by splat_last_error(); returns 1
+int splat_fail(const char *fmt, ...);
+
+// Launch-side entry points implemented in the .cu files --------------------------------
+struct FwdParams {
+  int P, W, H;
+  float scale_modifier;
+  int prefiltered;
+  const float *means3D, *opacities, *scales, *rotations, *transMat_precomp;
+  const float *viewmatrix, *projmatrix;
+  float *out_maps;
+  int *radii;
+};
+
+void launch_preprocess(const FwdParams &p, const GeomView &g, const ImageView &im,
+                       cudaStream_t s);
+void launch_chunk_scan(const GeomView &g, cudaStream_t s);
+void launch_emit(const FwdParams &p, const GeomView &g, const ImageView &im,
+                 const BinView &b, const SortPlan &sp, uint32_t capacity,
+                 cudaStream_t s);
+void launch_sort(const GeomView &g, const ImageView &im, const BinView &b,
+                 const SortPlan &sp, uint32_t capacity, cudaStream_t s);
+void launch_digit_scan(const uint32_t *hist, uint32_t *digit_base, int npass, uint2 *ranges,
+                       int tiles, int tile_pass_single, cudaStream_t s);
+unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long *b,
+                                       unsigned long long *keys_out, uint32_t *plist_out,
+                                       const uint32_t *num_ptr, uint32_t capacity,
+                                       uint32_t *status, const size_t *status_off,
+                                       uint32_t *tickets, const uint32_t *digit_base,
+                                       int npass, const int *shift, const int *bits,
+                                       int unpack_last, int idx_bits, int nblk,
+                                       cudaStream_t s);
+void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageView &im,
+                           const BinView &b, uint32_t capacity, cudaStream_t s);
+
+struct BwdParams {
+  int P, W, H;
+  const float *scales, *rotations, *viewmatrix, *projmatrix;
+  const int *radii;
+  const float *dL_dout;
+  float *dL_dmeans2D, *dL_dnormal, *dL_dopacity, *dL_dmeans3D, *dL_dtransMat,
+      *dL_dscales, *dL_drotations;
+};
+void launch_render_backward(const BwdParams &p, const GeomView &g, const ImageView &im,
+                            const BinView &b, cudaStream_t s);
+void launch_backward_preprocess(const BwdParams &p, cudaStream_t s);
+void launch_mark_visible(int P, const float *means3D, const float *viewmatrix,
+                         unsigned char *present, cudaStream_t s);
+void launch_unpack_debug(const GeomView &g, int P, float *transMat, float *normal_opacity,
+                         cudaStream_t s);
+
+// Exactly-rounded single operations: the compiler must not re-associate or contract
+// these, they pin the reference's compiled arithmetic (see DESIGN.md "bit-exactness").
+#define FM(a, b) __fmul_rn((a), (b))
+#define FA(a, b) __fadd_rn((a), (b))
+#define FS(a, b) __fsub_rn((a), (b))
+#define FF(a, b, c) __fmaf_rn((a), (b), (c))

@@ -1,0 +1,267 @@
+// dssr_api.cu — the C-ABI of the rasterizer (include/splat_b200.h): argument checks,
+// buffer carving and kernel sequencing.  Mirrors the host side of
+// CudaRasterizer::Rasterizer::forward / backward / markVisible
+// (submodules/diff-surfel-spherical-rasterization/cuda_rasterizer/rasterizer_impl.cu:
+// 117-122, 170-262, 266-313).
+#include <cstdarg>
+#include <cstring>
+#include <string>
+
+#include "../../include/splat_b200.h"
+#include "common.cuh"
+
+static thread_local std::string g_err;
+
+namespace {
+
+thread_local uint32_t *g_pinned = nullptr;      // 2 words: num_rendered, status
+thread_local cudaEvent_t g_event = nullptr;
+
+#define fail splat_fail
+
+#define CUDA_TRY(expr)                                                        \
+  do {                                                                        \
+    cudaError_t e_ = (expr);                                                  \
+    if (e_ != cudaSuccess)                                                    \
+      return fail("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_),     \
+                  __FILE__, __LINE__);                                        \
+  } while (0)
+
+// CHECK_CUDA (auxiliary.h:368-377): with debug, synchronise and check after a launch.
+#define LAUNCH_CHECK(debug, stream, what)                                     \
+  do {                                                                        \
+    cudaError_t e_ = cudaGetLastError();                                      \
+    if (e_ == cudaSuccess && (debug)) e_ = cudaStreamSynchronize(stream);     \
+    if (e_ != cudaSuccess)                                                    \
+      return fail("[CUDA ERROR] in %s: %s", what, cudaGetErrorString(e_));    \
+  } while (0)
+
+int ensure_host_scratch() {
+  if (!g_pinned) CUDA_TRY(cudaHostAlloc((void **)&g_pinned, 64, cudaHostAllocPortable));
+  if (!g_event) CUDA_TRY(cudaEventCreateWithFlags(&g_event, cudaEventDisableTiming));
+  return 0;
+}
+
+int run_binning_and_render(const dssr_forward_args *a, const FwdParams &fp,
+                           const GeomView &gv, const ImageView &iv, const SortPlan &sp,
+                           uint32_t capacity, cudaStream_t st) {
+  const int keep = (a->debug & 2) ? 1 : 0;
+  const bool dbg = a->debug & 1;
+  BinLayout bl(capacity, keep, sp);
+  char *bptr = a->binning_alloc(a->binning_ctx, bl.total);
+  if (!bptr) return fail("binning_alloc(%zu) returned NULL", bl.total);
+  BinView bv = make_bin_view(bptr, capacity, keep, sp);
+  BinHeader bh;
+  memset(&bh, 0, sizeof bh);
+  bh.magic = 0x42494e31u;
+  bh.capacity = capacity;
+  bh.keep_unsorted = keep;
+  CUDA_TRY(cudaMemcpyAsync(bv.hdr, &bh, sizeof bh, cudaMemcpyHostToDevice, st));
+  CUDA_TRY(cudaMemsetAsync(bv.hist, 0, bv.zero_bytes, st));
+  launch_emit(fp, gv, iv, bv, sp, capacity, st);
+  LAUNCH_CHECK(dbg, st, "emit");
+  launch_sort(gv, iv, bv, sp, capacity, st);
+  LAUNCH_CHECK(dbg, st, "sort");
+  launch_render_forward(fp, gv, iv, bv, capacity, st);
+  LAUNCH_CHECK(dbg, st, "render_forward");
+  return 0;
+}
+
+}  // namespace
+
+int splat_fail(const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return 1;
+}
+
+extern "C" {
+
+const char *splat_last_error(void) { return g_err.c_str(); }
+int splat_abi_version(void) { return 1; }
+
+size_t dssr_geometry_bytes(int P) { return GeomLayout(P < 0 ? 0 : P).total; }
+size_t dssr_image_bytes(int W, int H) { return ImageLayout(W, H).total; }
+size_t dssr_binning_bytes(int64_t capacity, int W, int H, int P, int keep_unsorted) {
+  ImageLayout il(W, H);
+  SortPlan sp(P, il.tiles);
+  return BinLayout((size_t)(capacity < 0 ? 0 : capacity), keep_unsorted, sp).total;
+}
+
+int dssr_forward(const dssr_forward_args *a, int *num_rendered) {
+  if (!a || !num_rendered) return fail("dssr_forward: NULL argument");
+  *num_rendered = 0;
+  if (a->P < 0 || a->W <= 0 || a->H <= 0) return fail("dssr_forward: bad sizes P=%d W=%d H=%d", a->P, a->W, a->H);
+  if (!a->out_maps) return fail("dssr_forward: out_maps is NULL");
+  cudaStream_t st = (cudaStream_t)a->stream;
+  const size_t HW = (size_t)a->W * a->H;
+  if (a->P == 0) {  // rasterize_points.cu:73: nothing launched, zeros returned
+    CUDA_TRY(cudaMemsetAsync(a->out_maps, 0, 7 * HW * sizeof(float), st));
+    return 0;
+  }
+  if (!a->means3D || !a->opacities || !a->viewmatrix || !a->projmatrix || !a->radii)
+    return fail("dssr_forward: NULL input pointer");
+  const bool precomp = a->transMat_precomp != nullptr;
+  if (!precomp && (!a->scales || !a->rotations))
+    return fail("dssr_forward: need scales+rotations or transMat_precomp");
+  if (!a->geom_alloc || !a->binning_alloc || !a->image_alloc)
+    return fail("dssr_forward: NULL allocator callback");
+  if (ensure_host_scratch()) return 1;
+  const bool dbg = a->debug & 1;
+
+  GeomLayout gl(a->P);
+  ImageLayout il(a->W, a->H);
+  SortPlan sp(a->P, il.tiles);
+  if (!sp.ok)
+    return fail("dssr_forward: P=%d with %d tiles does not fit the 64-bit sort word", a->P, il.tiles);
+  char *gptr = a->geom_alloc(a->geom_ctx, gl.total);
+  if (!gptr) return fail("geom_alloc(%zu) returned NULL", gl.total);
+  char *iptr = a->image_alloc(a->image_ctx, il.total);
+  if (!iptr) return fail("image_alloc(%zu) returned NULL", il.total);
+  GeomView gv = make_geom_view(gptr, a->P);
+  ImageView iv = make_image_view(iptr, a->W, a->H);
+
+  FwdParams fp;
+  fp.P = a->P; fp.W = a->W; fp.H = a->H;
+  fp.scale_modifier = a->scale_modifier;
+  fp.prefiltered = a->prefiltered;
+  fp.means3D = a->means3D; fp.opacities = a->opacities;
+  fp.scales = a->scales; fp.rotations = a->rotations;
+  fp.transMat_precomp = a->transMat_precomp;
+  fp.viewmatrix = a->viewmatrix; fp.projmatrix = a->projmatrix;
+  fp.out_maps = a->out_maps; fp.radii = a->radii;
+
+  GeomHeader gh;
+  memset(&gh, 0, sizeof gh);
+  gh.magic = 0x47454f31u;
+  gh.P = a->P; gh.W = a->W; gh.H = a->H;
+  CUDA_TRY(cudaMemcpyAsync(gv.hdr, &gh, sizeof gh, cudaMemcpyHostToDevice, st));
+  launch_preprocess(fp, gv, iv, st);
+  LAUNCH_CHECK(dbg, st, "preprocess");
+  launch_chunk_scan(gv, st);
+  LAUNCH_CHECK(dbg, st, "chunk_scan");
+  CUDA_TRY(cudaMemcpyAsync(g_pinned, &gv.hdr->num_rendered, 8, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaEventRecord(g_event, st));
+
+  // With a capacity hint the rest of the frame is enqueued BEFORE the host waits for
+  // the instance count (the reference blocks here: rasterizer_impl.cu:216-219).
+  int64_t hint = a->binning_hint;
+  if (hint > 0x3fffffff) hint = 0x3fffffff;
+  if (hint > 0)
+    if (run_binning_and_render(a, fp, gv, iv, sp, (uint32_t)hint, st)) return 1;
+  CUDA_TRY(cudaEventSynchronize(g_event));
+  const uint32_t N = g_pinned[0], status = g_pinned[1];
+  if (status & 1u)
+    return fail("Point is filtered although prefiltered is set. This shouldn't happen!");
+  if (N > 0x3fffffffu) return fail("dssr_forward: %u instances exceed the 2^30 limit", N);
+  if (hint <= 0 || (int64_t)N > hint)
+    if (run_binning_and_render(a, fp, gv, iv, sp, N, st)) return 1;
+  *num_rendered = (int)N;
+  return 0;
+}
+
+int dssr_backward(const dssr_backward_args *a) {
+  if (!a) return fail("dssr_backward: NULL argument");
+  if (a->P < 0 || a->W <= 0 || a->H <= 0) return fail("dssr_backward: bad sizes");
+  cudaStream_t st = (cudaStream_t)a->stream;
+  const size_t P = (size_t)a->P;
+  if (!a->dL_dmeans2D || !a->dL_dnormal || !a->dL_dopacity || !a->dL_dmeans3D ||
+      !a->dL_dtransMat || !a->dL_dscales || !a->dL_drotations)
+    return fail("dssr_backward: NULL gradient output");
+  if (P == 0) return 0;
+  if (!a->geom_buffer || !a->binning_buffer || !a->image_buffer || !a->dL_dout ||
+      !a->radii || !a->viewmatrix || !a->projmatrix)
+    return fail("dssr_backward: NULL input pointer");
+  const bool dbg = a->debug & 1;
+  CUDA_TRY(cudaMemsetAsync(a->dL_dmeans2D, 0, 12 * P, st));
+  CUDA_TRY(cudaMemsetAsync(a->dL_dnormal, 0, 12 * P, st));
+  CUDA_TRY(cudaMemsetAsync(a->dL_dopacity, 0, 4 * P, st));
+  CUDA_TRY(cudaMemsetAsync(a->dL_dtransMat, 0, 48 * P, st));
+  ImageLayout il(a->W, a->H);
+  SortPlan sp(a->P, il.tiles);
+  GeomView gv = make_geom_view(a->geom_buffer, a->P);
+  ImageView iv = make_image_view(a->image_buffer, a->W, a->H);
+  BinView bv = make_bin_view(a->binning_buffer, (size_t)a->R, 0, sp);  // only point_list is used
+  BwdParams bp;
+  bp.P = a->P; bp.W = a->W; bp.H = a->H;
+  bp.scales = a->scales; bp.rotations = a->rotations;
+  bp.viewmatrix = a->viewmatrix; bp.projmatrix = a->projmatrix;
+  bp.radii = a->radii; bp.dL_dout = a->dL_dout;
+  bp.dL_dmeans2D = a->dL_dmeans2D; bp.dL_dnormal = a->dL_dnormal;
+  bp.dL_dopacity = a->dL_dopacity; bp.dL_dmeans3D = a->dL_dmeans3D;
+  bp.dL_dtransMat = a->dL_dtransMat; bp.dL_dscales = a->dL_dscales;
+  bp.dL_drotations = a->dL_drotations;
+  launch_render_backward(bp, gv, iv, bv, st);
+  LAUNCH_CHECK(dbg, st, "render_backward");
+  launch_backward_preprocess(bp, st);
+  LAUNCH_CHECK(dbg, st, "backward_preprocess");
+  return 0;
+}
+
+int dssr_mark_visible(int P, const float *means3D, const float *viewmatrix,
+                      const float *projmatrix, unsigned char *present, void *stream) {
+  (void)projmatrix;
+  if (P < 0) return fail("dssr_mark_visible: P < 0");
+  if (P == 0) return 0;
+  if (!means3D || !viewmatrix || !present) return fail("dssr_mark_visible: NULL pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  launch_mark_visible(P, means3D, viewmatrix, present, st);
+  LAUNCH_CHECK(false, st, "mark_visible");
+  return 0;
+}
+
+int dssr_debug_state(const char *geom_buffer, const char *binning_buffer,
+                     const char *image_buffer, const char *name, float *scratch,
+                     void **ptr, size_t *count, void *stream) {
+  if (!geom_buffer || !image_buffer || !name || !ptr || !count)
+    return fail("dssr_debug_state: NULL argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  GeomHeader gh;
+  CUDA_TRY(cudaStreamSynchronize(st));
+  CUDA_TRY(cudaMemcpy(&gh, align_ptr(geom_buffer), sizeof gh, cudaMemcpyDeviceToHost));
+  if (gh.magic != 0x47454f31u) return fail("dssr_debug_state: not a geometry buffer");
+  const int P = gh.P, W = gh.W, H = gh.H;
+  const size_t R = gh.num_rendered, HW = (size_t)W * H;
+  GeomView gv = make_geom_view(geom_buffer, P);
+  ImageView iv = make_image_view(image_buffer, W, H);
+  SortPlan sp(P, iv.tiles);
+  BinView bv;
+  memset(&bv, 0, sizeof bv);
+  if (binning_buffer) {
+    BinHeader bh;
+    CUDA_TRY(cudaMemcpy(&bh, align_ptr(binning_buffer), sizeof bh, cudaMemcpyDeviceToHost));
+    if (bh.magic != 0x42494e31u) return fail("dssr_debug_state: not a binning buffer");
+    bv = make_bin_view(binning_buffer, bh.capacity, bh.keep_unsorted, sp);
+  }
+  const std::string n(name);
+  if (n == "depths") { *ptr = gv.depths; *count = P; }
+  else if (n == "means2D") { *ptr = gv.xy; *count = 2 * (size_t)P; }
+  else if (n == "tiles_touched") { *ptr = gv.tiles; *count = P; }
+  else if (n == "point_offsets") { *ptr = gv.offsets; *count = P; }
+  else if (n == "transMat" || n == "normal_opacity") {
+    if (!scratch) return fail("dssr_debug_state: %s needs scratch", name);
+    launch_unpack_debug(gv, P, scratch, scratch + 12 * (size_t)P, st);
+    CUDA_TRY(cudaStreamSynchronize(st));
+    if (n == "transMat") { *ptr = scratch; *count = 12 * (size_t)P; }
+    else { *ptr = scratch + 12 * (size_t)P; *count = 4 * (size_t)P; }
+  }
+  else if (n == "keys") { *ptr = bv.keys; *count = R; }
+  else if (n == "point_list") { *ptr = bv.point_list; *count = R; }
+  else if (n == "keys_unsorted") {
+    if (!bv.keys_unsorted) return fail("dssr_debug_state: forward ran without debug bit1");
+    *ptr = bv.keys_unsorted; *count = R;
+  }
+  else if (n == "ranges") { *ptr = iv.ranges; *count = 2 * (size_t)iv.tiles; }
+  else if (n == "final_T") { *ptr = iv.final_T; *count = 3 * HW; }
+  else if (n == "n_contrib") { *ptr = iv.n_contrib; *count = 2 * HW; }
+  else return fail("dssr_debug_state: unknown array '%s'", name);
+  if ((n == "keys" || n == "point_list") && !binning_buffer)
+    return fail("dssr_debug_state: %s needs the binning buffer", name);
+  return 0;
+}
+
+}  // extern "C"

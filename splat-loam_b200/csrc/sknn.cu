@@ -1,0 +1,307 @@
+// sknn.cu — distCUDA2: mean squared distance to the 3 nearest neighbours.
+//
+// Replaces SimpleKNN::knn, submodules/simple-knn/simple_knn.cu:186-222 (coord2Morton
+// :46-71, boxMinMax :79-118, distBoxPoint :120-130, updateKBest :132-146, boxMeanDist
+// :148-184), called from distCUDA2 (submodules/simple-knn/spatial.cu:15-26).
+//
+// The reference sorts the points by 30-bit Morton code, cuts the sorted order into
+// boxes of 1024 points and lets EVERY point test EVERY box (P/1024 box tests per point,
+// 1024 distance evaluations per surviving box).  Its pruning is conservative, so what
+// it returns is the exact 3-NN; any exact 3-NN search that evaluates a distance as
+//   d = p - q;  dist = fma(d.z, d.z, fma(d.x, d.x, d.y*d.y))      (the compiled form)
+// and keeps the three smallest returns the same floats.  Here: same Morton order (our
+// own radix sort), but an implicit 8-ary box hierarchy over 32-point leaves that each
+// point descends with a small stack, so the work per point is O(log P) box tests and
+// a handful of leaves, and no cudaMalloc / host round trip happens inside the call.
+#include <cfloat>
+
+#include "../../include/splat_b200.h"
+#include "common.cuh"
+
+namespace {
+
+constexpr int LEAF = 32;
+constexpr int FAN = 8;
+constexpr int MAXL = 12;
+constexpr int BB_BLOCKS = 256;
+
+struct KnnLayout {
+  size_t hdr, partial, words_a, words_b, sorted, boxes, hist, tickets, status, digit_base,
+      total, zero_bytes;
+  size_t status_off[SORT_MAX_PASSES];
+  int nblk, nlevel;
+  uint32_t cnt[MAXL];
+  size_t box_off[MAXL];  // in nodes
+  __host__ explicit KnnLayout(int P) {
+    nblk = (P + SORT_BLOCK_ELEMS - 1) / SORT_BLOCK_ELEMS;
+    if (nblk < 1) nblk = 1;
+    nlevel = 0;
+    uint32_t c = (uint32_t)((P + LEAF - 1) / LEAF);
+    if (c < 1) c = 1;
+    size_t nodes = 0;
+    while (true) {
+      cnt[nlevel] = c;
+      box_off[nlevel] = nodes;
+      nodes += c;
+      nlevel++;
+      if (c <= FAN || nlevel == MAXL) break;
+      c = (c + FAN - 1) / FAN;
+    }
+    size_t o = 0;
+    hdr = o;      o = align_up(o + 256, 256);
+    partial = o;  o = align_up(o + (size_t)(BB_BLOCKS + 1) * 6 * 4, 256);
+    words_a = o;  o = align_up(o + (size_t)P * 8, 256);
+    words_b = o;  o = align_up(o + (size_t)P * 8, 256);
+    sorted = o;   o = align_up(o + (size_t)P * 16, 256);
+    boxes = o;    o = align_up(o + nodes * 32, 256);
+    hist = o;     o = align_up(o + (size_t)3 * SORT_MAX_BINS * 4, 256);
+    tickets = o;  o = align_up(o + 64, 256);
+    status = o;
+    for (int p = 0; p < SORT_MAX_PASSES; p++)
+      status_off[p] = (size_t)(p < 3 ? p : 0) * nblk * SORT_MAX_BINS;
+    o = align_up(o + (size_t)3 * nblk * SORT_MAX_BINS * 4, 256);
+    zero_bytes = o - hist;
+    digit_base = o; o = align_up(o + (size_t)3 * SORT_MAX_BINS * 4, 256);
+    total = o + 256;
+  }
+};
+
+struct KnnLevels {
+  int nlevel;
+  uint32_t cnt[MAXL];
+  uint32_t off[MAXL];
+};
+
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// cub::DeviceReduce with CustomMin / CustomMax and init (0,0,0) (simple_knn.cu:192-201)
+__global__ void __launch_bounds__(256)
+bbox_partial_kernel(int P, const float *__restrict__ pts, float *partial) {
+  __shared__ float s[8][6];
+  float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < P; i += gridDim.x * 256) {
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      float v = pts[3 * (size_t)i + c];
+      mn[c] = fminf(mn[c], v);
+      mx[c] = fmaxf(mx[c], v);
+    }
+  }
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+    float a = warp_min(mn[c]), b = warp_max(mx[c]);
+    if (lane == 0) {
+      s[wid][c] = a;
+      s[wid][3 + c] = b;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    float r = s[0][threadIdx.x];
+    for (int w = 1; w < 8; w++)
+      r = threadIdx.x < 3 ? fminf(r, s[w][threadIdx.x]) : fmaxf(r, s[w][threadIdx.x]);
+    partial[blockIdx.x * 6 + threadIdx.x] = r;
+  }
+}
+
+__global__ void bbox_final_kernel(int nblocks, float *partial, uint32_t *num, int P) {
+  const int c = threadIdx.x;
+  if (c < 6) {
+    float r = 0.0f;  // the reduction's init value: the origin is part of the box
+    for (int b = 0; b < nblocks; b++)
+      r = c < 3 ? fminf(r, partial[b * 6 + c]) : fmaxf(r, partial[b * 6 + c]);
+    partial[BB_BLOCKS * 6 + c] = r;
+  }
+  if (c == 6) *num = (uint32_t)P;
+}
+
+// prepMorton / coord2Morton (simple_knn.cu:46-62)
+__device__ __forceinline__ uint32_t prep_morton(uint32_t x) {
+  x = (x | (x << 16)) & 0x030000FF;
+  x = (x | (x << 8)) & 0x0300F00F;
+  x = (x | (x << 4)) & 0x030C30C3;
+  x = (x | (x << 2)) & 0x09249249;
+  return x;
+}
+
+__global__ void __launch_bounds__(256)
+morton_kernel(int P, const float *__restrict__ pts, const float *__restrict__ bbox,
+              unsigned long long *words, uint32_t *hist) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= P) return;
+  const float mnx = bbox[0], mny = bbox[1], mnz = bbox[2];
+  const float mxx = bbox[3], mxy = bbox[4], mxz = bbox[5];
+  const float x = pts[3 * (size_t)i], y = pts[3 * (size_t)i + 1], z = pts[3 * (size_t)i + 2];
+  uint32_t cx = prep_morton((uint32_t)(__fdiv_rn(x - mnx, mxx - mnx) * 1023.0f));
+  uint32_t cy = prep_morton((uint32_t)(__fdiv_rn(y - mny, mxy - mny) * 1023.0f));
+  uint32_t cz = prep_morton((uint32_t)(__fdiv_rn(z - mnz, mxz - mnz) * 1023.0f));
+  const uint32_t code = (cx | (cy << 1) | (cz << 2)) & 0x3fffffffu;
+  words[i] = ((unsigned long long)code << 32) | (uint32_t)i;
+  atomicAdd(&hist[0 * SORT_MAX_BINS + (code & 1023u)], 1u);
+  atomicAdd(&hist[1 * SORT_MAX_BINS + ((code >> 10) & 1023u)], 1u);
+  atomicAdd(&hist[2 * SORT_MAX_BINS + (code >> 20)], 1u);
+}
+
+// sorted order -> float4(x, y, z, bits(original index)) and the 32-point leaf boxes
+__global__ void __launch_bounds__(256)
+gather_leaf_kernel(int P, const float *__restrict__ pts,
+                   const unsigned long long *__restrict__ words, float4 *sorted,
+                   float4 *boxes) {
+  const int i = blockIdx.x * 256 + threadIdx.x;  // grid covers whole leaves
+  float x = 0.f, y = 0.f, z = 0.f;
+  const bool have = i < P;
+  if (have) {
+    const uint32_t idx = (uint32_t)words[i];
+    x = pts[3 * (size_t)idx];
+    y = pts[3 * (size_t)idx + 1];
+    z = pts[3 * (size_t)idx + 2];
+    sorted[i] = make_float4(x, y, z, __uint_as_float(idx));
+  }
+  const float lx = warp_min(have ? x : FLT_MAX), ly = warp_min(have ? y : FLT_MAX),
+              lz = warp_min(have ? z : FLT_MAX);
+  const float hx = warp_max(have ? x : -FLT_MAX), hy = warp_max(have ? y : -FLT_MAX),
+              hz = warp_max(have ? z : -FLT_MAX);
+  if ((threadIdx.x & 31) == 0 && have) {
+    boxes[2 * (size_t)(i >> 5)] = make_float4(lx, ly, lz, 0.f);
+    boxes[2 * (size_t)(i >> 5) + 1] = make_float4(hx, hy, hz, 0.f);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+level_kernel(uint32_t n, uint32_t nchild, const float4 *__restrict__ child, float4 *node) {
+  const uint32_t i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= n) return;
+  float4 lo = make_float4(FLT_MAX, FLT_MAX, FLT_MAX, 0.f);
+  float4 hi = make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, 0.f);
+  for (uint32_t c = i * FAN; c < min(i * FAN + FAN, nchild); c++) {
+    const float4 a = child[2 * (size_t)c], b = child[2 * (size_t)c + 1];
+    lo.x = fminf(lo.x, a.x); lo.y = fminf(lo.y, a.y); lo.z = fminf(lo.z, a.z);
+    hi.x = fmaxf(hi.x, b.x); hi.y = fmaxf(hi.y, b.y); hi.z = fmaxf(hi.z, b.z);
+  }
+  node[2 * (size_t)i] = lo;
+  node[2 * (size_t)i + 1] = hi;
+}
+
+// updateKBest<3> (simple_knn.cu:132-146) with the distance in its compiled form
+__device__ __forceinline__ void update3(const float4 &q, const float4 &p, float &b0, float &b1,
+                                        float &b2) {
+  const float dx = FS(p.x, q.x), dy = FS(p.y, q.y), dz = FS(p.z, q.z);
+  float dist = FF(dz, dz, FF(dx, dx, FM(dy, dy)));
+  if (b0 > dist) { float t = b0; b0 = dist; dist = t; }
+  if (b1 > dist) { float t = b1; b1 = dist; dist = t; }
+  if (b2 > dist) { b2 = dist; }
+}
+
+__global__ void __launch_bounds__(128)
+query_kernel(int P, const float4 *__restrict__ sorted, const float4 *__restrict__ boxes,
+             KnnLevels lv, float *__restrict__ out) {
+  const int i = blockIdx.x * 128 + threadIdx.x;
+  if (i >= P) return;
+  const float4 q = sorted[i];
+  float b0 = FLT_MAX, b1 = FLT_MAX, b2 = FLT_MAX;
+  const uint32_t own = (uint32_t)i >> 5;
+  {  // own leaf first: it tightens the bound before the descent
+    const int s = own * LEAF, e = min(P, s + LEAF);
+    for (int j = s; j < e; j++)
+      if (j != i) update3(q, sorted[j], b0, b1, b2);
+  }
+  uint32_t cur[MAXL], end[MAXL];
+  int lvl = lv.nlevel - 1;
+  cur[lvl] = 0;
+  end[lvl] = lv.cnt[lvl];
+  const int top = lvl;
+  while (lvl <= top) {
+    if (cur[lvl] >= end[lvl]) {
+      lvl++;
+      continue;
+    }
+    const uint32_t n = cur[lvl]++;
+    if (lvl == 0 && n == own) continue;
+    const float4 lo = boxes[2 * (size_t)(lv.off[lvl] + n)];
+    const float4 hi = boxes[2 * (size_t)(lv.off[lvl] + n) + 1];
+    const float ex = fmaxf(0.f, fmaxf(lo.x - q.x, q.x - hi.x));
+    const float ey = fmaxf(0.f, fmaxf(lo.y - q.y, q.y - hi.y));
+    const float ez = fmaxf(0.f, fmaxf(lo.z - q.z, q.z - hi.z));
+    const float d = ex * ex + ey * ey + ez * ez;
+    // slack covers the rounding of d against the rounding of a candidate distance
+    if (d > b2 * 1.000001f) continue;
+    if (lvl == 0) {
+      const int s = n * LEAF, e = min(P, s + LEAF);
+      for (int j = s; j < e; j++) update3(q, sorted[j], b0, b1, b2);
+    } else {
+      lvl--;
+      cur[lvl] = n * FAN;
+      end[lvl] = min(n * FAN + FAN, lv.cnt[lvl]);
+    }
+  }
+  out[__float_as_uint(q.w)] = (b0 + b1 + b2) / 3.0f;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t sknn_workspace_bytes(int P) { return KnnLayout(P < 0 ? 0 : P).total; }
+
+int sknn_dist2(int P, const float *points, float *mean_dists, void *workspace,
+               size_t workspace_bytes, void *stream) {
+  if (P < 0) return splat_fail("sknn_dist2: P < 0");
+  if (P == 0) return 0;
+  if (!points || !mean_dists || !workspace) return splat_fail("sknn_dist2: NULL pointer");
+  KnnLayout L(P);
+  if (workspace_bytes < L.total)
+    return splat_fail("sknn_dist2: workspace too small (%zu < %zu)", workspace_bytes, L.total);
+  cudaStream_t st = (cudaStream_t)stream;
+  char *w = align_ptr((const char *)workspace);
+  uint32_t *num = (uint32_t *)(w + L.hdr);
+  float *partial = (float *)(w + L.partial);
+  unsigned long long *wa = (unsigned long long *)(w + L.words_a);
+  unsigned long long *wb = (unsigned long long *)(w + L.words_b);
+  float4 *sorted = (float4 *)(w + L.sorted);
+  float4 *boxes = (float4 *)(w + L.boxes);
+  uint32_t *hist = (uint32_t *)(w + L.hist);
+  uint32_t *tickets = (uint32_t *)(w + L.tickets);
+  uint32_t *status = (uint32_t *)(w + L.status);
+  uint32_t *digit_base = (uint32_t *)(w + L.digit_base);
+
+  if (cudaMemsetAsync(hist, 0, L.zero_bytes, st) != cudaSuccess)
+    return splat_fail("sknn_dist2: memset failed: %s", cudaGetErrorString(cudaGetLastError()));
+  int bb = (P + 255) / 256;
+  if (bb > BB_BLOCKS) bb = BB_BLOCKS;
+  bbox_partial_kernel<<<bb, 256, 0, st>>>(P, points, partial);
+  bbox_final_kernel<<<1, 32, 0, st>>>(bb, partial, num, P);
+  morton_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, points, partial + BB_BLOCKS * 6, wa, hist);
+  launch_digit_scan(hist, digit_base, 3, nullptr, 0, -1, st);
+  const int shift[3] = {32, 42, 52}, bits[3] = {10, 10, 10};
+  unsigned long long *res = launch_sort_passes(wa, wb, nullptr, nullptr, num, (uint32_t)P, status,
+                                               L.status_off, tickets, digit_base, 3, shift, bits,
+                                               0, 32, L.nblk, st);
+  const int leaves = (P + LEAF - 1) / LEAF;
+  gather_leaf_kernel<<<(leaves * LEAF + 255) / 256, 256, 0, st>>>(P, points, res, sorted, boxes);
+  KnnLevels lv;
+  lv.nlevel = L.nlevel;
+  for (int l = 0; l < L.nlevel; l++) {
+    lv.cnt[l] = L.cnt[l];
+    lv.off[l] = (uint32_t)L.box_off[l];
+  }
+  for (int l = 1; l < L.nlevel; l++)
+    level_kernel<<<(L.cnt[l] + 255) / 256, 256, 0, st>>>(L.cnt[l], L.cnt[l - 1],
+                                                         boxes + 2 * L.box_off[l - 1],
+                                                         boxes + 2 * L.box_off[l]);
+  query_kernel<<<(P + 127) / 128, 128, 0, st>>>(P, sorted, boxes, lv, mean_dists);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return splat_fail("sknn_dist2: launch failed: %s", cudaGetErrorString(e));
+  return 0;
+}
+
+}  // extern "C"

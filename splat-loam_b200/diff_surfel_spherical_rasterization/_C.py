@@ -1,0 +1,160 @@
+"""`_C` of the drop-in package: same three functions, argument order and tuple layouts
+as the reference's pybind module (submodules/diff-surfel-spherical-rasterization/
+ext.cpp:5-9, rasterize_points.cu:32-165), implemented as a thin ctypes layer over the
+C-ABI (include/splat_b200.h).  PyTorch is used for device memory and streams only.
+"""
+import ctypes
+import os
+
+import torch
+
+import splat_b200_native as _n
+
+_lib = _n.load()
+
+# Capacity hints for the binning buffer, keyed by (device, P, H, W): with a hint the
+# whole frame is enqueued before the host reads the instance count, so the per-forward
+# host<->device round trip of the reference (rasterizer_impl.cu:216-219) does not stall
+# the GPU.  SPLAT_B200_HINT=0 restores the exact-size two-phase behaviour.
+_USE_HINT = os.environ.get("SPLAT_B200_HINT", "1") != "0"
+_hints = {}
+
+
+def _check_cuda(t, name):
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor")
+
+
+def _f32(t):
+    t = t.contiguous()
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t
+
+
+def _ptr(t):
+    return t.data_ptr() if t.numel() else None
+
+
+class _Grower:
+    """Allocator callback state: one growable uint8 tensor (resizeFunctional,
+    rasterize_points.cu:24-30)."""
+
+    def __init__(self, device):
+        self.tensor = torch.empty(0, dtype=torch.uint8, device=device)
+        self.cb = _n.ALLOC_FN(self._alloc)
+
+    def _alloc(self, _ctx, nbytes):
+        if self.tensor.numel() < nbytes:
+            self.tensor = torch.empty(int(nbytes), dtype=torch.uint8, device=self.tensor.device)
+        return self.tensor.data_ptr()
+
+
+def rasterize_gaussians(means3D, opacity, scales, rotations, scale_modifier, transMat_precomp,
+                        viewmatrix, projmatrix, image_height, image_width, prefiltered, debug):
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    for t, nm in ((means3D, "means3D"), (opacity, "opacity"), (scales, "scales"),
+                  (rotations, "rotations"), (transMat_precomp, "transMat_precomp"),
+                  (viewmatrix, "viewmatrix"), (projmatrix, "projmatrix")):
+        _check_cuda(t, nm)
+    P, H, W = int(means3D.size(0)), int(image_height), int(image_width)
+    dev = means3D.device
+    with torch.cuda.device(dev):
+        out = torch.empty((7, H, W), dtype=torch.float32, device=dev)
+        radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        geom, binning, img = _Grower(dev), _Grower(dev), _Grower(dev)
+        means3D_c, opacity_c = _f32(means3D), _f32(opacity)
+        scales_c, rot_c, pre_c = _f32(scales), _f32(rotations), _f32(transMat_precomp)
+        view_c, proj_c = _f32(viewmatrix), _f32(projmatrix)
+        key = (dev.index, P, H, W)
+        hint = _hints.get(key, 0) if _USE_HINT else 0
+        a = _n.DssrForwardArgs(
+            P, W, H, float(scale_modifier), int(bool(prefiltered)), int(bool(debug)),
+            _ptr(means3D_c), _ptr(opacity_c), _ptr(scales_c), _ptr(rot_c), _ptr(pre_c),
+            _ptr(view_c), _ptr(proj_c), _ptr(out), _ptr(radii),
+            geom.cb, None, binning.cb, None, img.cb, None, hint,
+            torch.cuda.current_stream(dev).cuda_stream)
+        n = ctypes.c_int(0)
+        _n.check(_lib.dssr_forward(ctypes.byref(a), ctypes.byref(n)))
+        if _USE_HINT:
+            _hints[key] = int(n.value * 1.25) + 4096
+    return n.value, out, radii, geom.tensor, binning.tensor, img.tensor
+
+
+def rasterize_gaussians_backward(means3D, radii, scales, rotations, scale_modifier,
+                                 transMat_precomp, viewmatrix, projmatrix, dL_dout, geomBuffer,
+                                 R, binningBuffer, imageBuffer, debug):
+    for t, nm in ((means3D, "means3D"), (radii, "radii"), (scales, "scales"),
+                  (rotations, "rotations"), (transMat_precomp, "transMat_precomp"),
+                  (viewmatrix, "viewmatrix"), (projmatrix, "projmatrix"),
+                  (binningBuffer, "binningBuffer"), (imageBuffer, "imageBuffer"),
+                  (geomBuffer, "geomBuffer")):
+        _check_cuda(t, nm)
+    P = int(means3D.size(0))
+    H, W = int(dL_dout.size(1)), int(dL_dout.size(2))
+    dev = means3D.device
+    with torch.cuda.device(dev):
+        # one allocation, seven contiguous slices (the reference does seven torch::zeros,
+        # rasterize_points.cu:116-122; the kernels here write every element themselves)
+        flat = torch.empty(28 * P, dtype=torch.float32, device=dev)
+        cuts = (3, 3, 3, 1, 12, 2, 4)
+        views, o = [], 0
+        for c in cuts:
+            views.append(flat[o:o + c * P].view(P, c))
+            o += c * P
+        dmeans3D, dmeans2D, dnormal, dopacity, dtrans, dscales, drot = views
+        if P:
+            means3D_c, scales_c, rot_c = _f32(means3D), _f32(scales), _f32(rotations)
+            pre_c, view_c, proj_c = _f32(transMat_precomp), _f32(viewmatrix), _f32(projmatrix)
+            dout_c = _f32(dL_dout)
+            radii_c = radii.contiguous()
+            a = _n.DssrBackwardArgs(
+                P, W, H, int(R), float(scale_modifier), int(bool(debug)),
+                _ptr(means3D_c), _ptr(scales_c), _ptr(rot_c), _ptr(pre_c),
+                _ptr(view_c), _ptr(proj_c), _ptr(radii_c),
+                _ptr(geomBuffer), _ptr(binningBuffer), _ptr(imageBuffer), _ptr(dout_c),
+                _ptr(dmeans2D), _ptr(dnormal), _ptr(dopacity), _ptr(dmeans3D), _ptr(dtrans),
+                _ptr(dscales), _ptr(drot), torch.cuda.current_stream(dev).cuda_stream)
+            _n.check(_lib.dssr_backward(ctypes.byref(a)))
+    return dmeans2D, dopacity, dmeans3D, dtrans, dscales, drot
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    P = int(means3D.size(0))
+    present = torch.zeros((P,), dtype=torch.bool, device=means3D.device)
+    if P:
+        with torch.cuda.device(means3D.device):
+            m, v, p = _f32(means3D), _f32(viewmatrix), _f32(projmatrix)
+            _n.check(_lib.dssr_mark_visible(P, _ptr(m), _ptr(v), _ptr(p), present.data_ptr(),
+                                            torch.cuda.current_stream().cuda_stream))
+    return present
+
+
+def debug_state(geomBuffer, binningBuffer, imageBuffer, name):
+    """Parity-test accessor (dssr_debug_state): returns a CPU copy of an internal array."""
+    import numpy as np
+    dev = geomBuffer.device
+    with torch.cuda.device(dev):
+        hdr = geomBuffer.cpu().numpy()
+        # P lives in the header; scratch for the unpacked transMat / normal_opacity
+        off = (-geomBuffer.data_ptr()) % 256
+        P = int(np.frombuffer(hdr[off + 4:off + 8].tobytes(), dtype=np.int32)[0])
+        scratch = torch.empty(16 * max(P, 1), dtype=torch.float32, device=dev)
+        ptr, cnt = ctypes.c_void_p(), ctypes.c_size_t()
+        _n.check(_lib.dssr_debug_state(
+            _ptr(geomBuffer), _ptr(binningBuffer) if binningBuffer is not None else None,
+            _ptr(imageBuffer), name.encode(), scratch.data_ptr(), ctypes.byref(ptr),
+            ctypes.byref(cnt), torch.cuda.current_stream().cuda_stream))
+        dtype = {"depths": torch.float32, "means2D": torch.float32, "transMat": torch.float32,
+                 "normal_opacity": torch.float32, "final_T": torch.float32,
+                 "keys": torch.int64, "keys_unsorted": torch.int64}.get(name, torch.int32)
+        n = cnt.value
+        out = torch.empty(n, dtype=dtype, device=dev)
+        if n:
+            cudart = torch.cuda.cudart()
+            torch.cuda.synchronize()
+            rc = cudart.cudaMemcpy(out.data_ptr(), ptr.value, n * out.element_size(), 3)
+            if int(rc) != 0:
+                raise RuntimeError(f"cudaMemcpy failed: {rc}")
+        return out.cpu()

@@ -1,0 +1,110 @@
+"""ctypes loader for the in-tree C-ABI library (splat-loam_b200/lib/libsplat_b200.so).
+
+There is deliberately NO fallback: if the CUDA library is missing the import fails.
+Declarations mirror include/splat_b200.h one to one.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libsplat_b200.so")
+
+c_float_p = ctypes.c_void_p  # raw device pointers travel as integers
+ALLOC_FN = ctypes.CFUNCTYPE(ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t)
+
+
+class DssrForwardArgs(ctypes.Structure):
+    _fields_ = [
+        ("P", ctypes.c_int), ("W", ctypes.c_int), ("H", ctypes.c_int),
+        ("scale_modifier", ctypes.c_float),
+        ("prefiltered", ctypes.c_int), ("debug", ctypes.c_int),
+        ("means3D", c_float_p), ("opacities", c_float_p), ("scales", c_float_p),
+        ("rotations", c_float_p), ("transMat_precomp", c_float_p),
+        ("viewmatrix", c_float_p), ("projmatrix", c_float_p),
+        ("out_maps", c_float_p), ("radii", ctypes.c_void_p),
+        ("geom_alloc", ALLOC_FN), ("geom_ctx", ctypes.c_void_p),
+        ("binning_alloc", ALLOC_FN), ("binning_ctx", ctypes.c_void_p),
+        ("image_alloc", ALLOC_FN), ("image_ctx", ctypes.c_void_p),
+        ("binning_hint", ctypes.c_int64),
+        ("stream", ctypes.c_void_p),
+    ]
+
+
+class DssrBackwardArgs(ctypes.Structure):
+    _fields_ = [
+        ("P", ctypes.c_int), ("W", ctypes.c_int), ("H", ctypes.c_int), ("R", ctypes.c_int),
+        ("scale_modifier", ctypes.c_float), ("debug", ctypes.c_int),
+        ("means3D", c_float_p), ("scales", c_float_p), ("rotations", c_float_p),
+        ("transMat_precomp", c_float_p),
+        ("viewmatrix", c_float_p), ("projmatrix", c_float_p),
+        ("radii", ctypes.c_void_p),
+        ("geom_buffer", ctypes.c_void_p), ("binning_buffer", ctypes.c_void_p),
+        ("image_buffer", ctypes.c_void_p),
+        ("dL_dout", c_float_p),
+        ("dL_dmeans2D", c_float_p), ("dL_dnormal", c_float_p), ("dL_dopacity", c_float_p),
+        ("dL_dmeans3D", c_float_p), ("dL_dtransMat", c_float_p), ("dL_dscales", c_float_p),
+        ("dL_drotations", c_float_p),
+        ("stream", ctypes.c_void_p),
+    ]
+
+
+# every symbol include/splat_b200.h declares
+EXPORTS = (
+    "dssr_forward", "dssr_backward", "dssr_mark_visible", "dssr_geometry_bytes",
+    "dssr_image_bytes", "dssr_binning_bytes", "dssr_debug_state", "sknn_workspace_bytes",
+    "sknn_dist2", "splat_last_error", "splat_abi_version",
+)
+
+_lib = None
+
+
+def load():
+    """Load the library once; raise if it has not been built (no CPU fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python splat-loam_b200/build.py` "
+            "(nvcc, sm_100a). There is no CPU or PyTorch fallback for this path.")
+    lib = ctypes.CDLL(LIB_PATH)
+    lib.dssr_forward.argtypes = [ctypes.POINTER(DssrForwardArgs), ctypes.POINTER(ctypes.c_int)]
+    lib.dssr_forward.restype = ctypes.c_int
+    lib.dssr_backward.argtypes = [ctypes.POINTER(DssrBackwardArgs)]
+    lib.dssr_backward.restype = ctypes.c_int
+    lib.dssr_mark_visible.argtypes = [ctypes.c_int, c_float_p, c_float_p, c_float_p,
+                                      ctypes.c_void_p, ctypes.c_void_p]
+    lib.dssr_mark_visible.restype = ctypes.c_int
+    lib.dssr_geometry_bytes.argtypes = [ctypes.c_int]
+    lib.dssr_geometry_bytes.restype = ctypes.c_size_t
+    lib.dssr_image_bytes.argtypes = [ctypes.c_int, ctypes.c_int]
+    lib.dssr_image_bytes.restype = ctypes.c_size_t
+    lib.dssr_binning_bytes.argtypes = [ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                       ctypes.c_int]
+    lib.dssr_binning_bytes.restype = ctypes.c_size_t
+    lib.dssr_debug_state.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                     ctypes.c_char_p, c_float_p,
+                                     ctypes.POINTER(ctypes.c_void_p),
+                                     ctypes.POINTER(ctypes.c_size_t), ctypes.c_void_p]
+    lib.dssr_debug_state.restype = ctypes.c_int
+    lib.sknn_workspace_bytes.argtypes = [ctypes.c_int]
+    lib.sknn_workspace_bytes.restype = ctypes.c_size_t
+    lib.sknn_dist2.argtypes = [ctypes.c_int, c_float_p, c_float_p, ctypes.c_void_p,
+                               ctypes.c_size_t, ctypes.c_void_p]
+    lib.sknn_dist2.restype = ctypes.c_int
+    lib.splat_last_error.argtypes = []
+    lib.splat_last_error.restype = ctypes.c_char_p
+    lib.splat_abi_version.argtypes = []
+    lib.splat_abi_version.restype = ctypes.c_int
+    _lib = lib
+    return lib
+
+
+def last_error():
+    msg = load().splat_last_error()
+    return msg.decode(errors="replace") if msg else "unknown error"
+
+
+def check(rc):
+    if rc != 0:
+        raise RuntimeError(last_error())

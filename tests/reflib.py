@@ -1,0 +1,146 @@
+"""ctypes access to oracle/_ref/libref_splat.so — the UNMODIFIED reference CUDA rasterizer
+and simple-knn built by oracle/Makefile (test infrastructure; never imported by the
+product).  Only usable on a machine with a GPU.  The reference launches on the legacy
+default stream and synchronises, so callers need no stream handling.
+"""
+import ctypes
+import os
+
+import torch
+
+_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_LIB = os.path.join(_ROOT, "oracle", "_ref", "libref_splat.so")
+
+_STATE_DTYPES = {
+    "depths": torch.float32, "means2D": torch.float32, "transMat": torch.float32,
+    "normal_opacity": torch.float32, "tiles_touched": torch.int32,
+    "point_offsets": torch.int32, "keys_unsorted": torch.int64, "keys": torch.int64,
+    "point_list_unsorted": torch.int32, "point_list": torch.int32, "ranges": torch.int32,
+    "final_T": torch.float32, "n_contrib": torch.int32,
+}
+
+
+def available():
+    return os.path.exists(REF_LIB) and torch.cuda.is_available()
+
+
+_lib = None
+
+
+def _load():
+    global _lib
+    if _lib is None:
+        lib = ctypes.CDLL(REF_LIB)
+        vp = ctypes.c_void_p
+        lib.ref_dssr_create.restype = vp
+        lib.ref_dssr_destroy.argtypes = [vp]
+        fwd_args = [vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp, vp, ctypes.c_float,
+                    vp, vp, vp, vp, ctypes.c_int, vp, vp]
+        lib.ref_dssr_forward.argtypes = fwd_args
+        lib.ref_dssr_forward.restype = ctypes.c_int
+        lib.ref_dssr_forward_nosync.argtypes = fwd_args
+        lib.ref_dssr_forward_nosync.restype = ctypes.c_int
+        bwd_args = [vp, vp, vp, ctypes.c_float, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+        lib.ref_dssr_backward.argtypes = bwd_args
+        lib.ref_dssr_backward.restype = ctypes.c_int
+        lib.ref_dssr_backward_nosync.argtypes = bwd_args
+        lib.ref_dssr_backward_nosync.restype = ctypes.c_int
+        lib.ref_dssr_state.argtypes = [vp, ctypes.c_char_p, ctypes.POINTER(vp),
+                                       ctypes.POINTER(ctypes.c_size_t)]
+        lib.ref_dssr_state.restype = ctypes.c_int
+        lib.ref_dssr_mark_visible.argtypes = [ctypes.c_int, vp, vp, vp, vp]
+        lib.ref_dssr_mark_visible.restype = ctypes.c_int
+        lib.ref_sknn_dist2.argtypes = [ctypes.c_int, vp, vp]
+        lib.ref_sknn_dist2.restype = ctypes.c_int
+        lib.ref_sknn_dist2_nosync.argtypes = [ctypes.c_int, vp, vp]
+        lib.ref_sknn_dist2_nosync.restype = ctypes.c_int
+        _lib = lib
+    return _lib
+
+
+def _p(t):
+    return t.data_ptr() if t is not None and t.numel() else None
+
+
+class RefRasterizer:
+    """One reference rasterizer instance (owns its geometry/binning/image chunks)."""
+
+    def __init__(self):
+        self.lib = _load()
+        self.h = self.lib.ref_dssr_create()
+        self.P = 0
+
+    def __del__(self):
+        try:
+            self.lib.ref_dssr_destroy(self.h)
+        except Exception:
+            pass
+
+    def forward(self, means3D, opacities, scales, rotations, viewmatrix, projmatrix, H, W,
+                scale_modifier=1.0, precomp=None, prefiltered=False, sync=True):
+        P = means3D.shape[0]
+        self.P, self.H, self.W = P, H, W
+        dev = means3D.device
+        out = torch.empty((7, H, W), dtype=torch.float32, device=dev)
+        radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        self._keep = (means3D, opacities, scales, rotations, viewmatrix, projmatrix, precomp)
+        fn = self.lib.ref_dssr_forward if sync else self.lib.ref_dssr_forward_nosync
+        torch.cuda.current_stream().synchronize() if sync else None
+        R = fn(self.h, P, W, H, _p(means3D), _p(opacities), _p(scales), float(scale_modifier),
+               _p(rotations), _p(precomp), _p(viewmatrix), _p(projmatrix), int(prefiltered),
+               _p(out), _p(radii))
+        if R < 0:
+            raise RuntimeError("reference forward failed")
+        self.radii = radii
+        return R, out, radii
+
+    def backward(self, dL_dout, scale_modifier=1.0, sync=True):
+        means3D, opacities, scales, rotations, viewmatrix, projmatrix, precomp = self._keep
+        P, dev = self.P, means3D.device
+        g = {k: torch.empty((P, c), dtype=torch.float32, device=dev)
+             for k, c in (("means2D", 3), ("normal", 3), ("opacity", 1), ("means3D", 3),
+                          ("transMat", 12), ("scales", 2), ("rotations", 4))}
+        fn = self.lib.ref_dssr_backward if sync else self.lib.ref_dssr_backward_nosync
+        rc = fn(self.h, _p(means3D), _p(scales), float(scale_modifier), _p(rotations),
+                _p(precomp), _p(viewmatrix), _p(projmatrix), _p(self.radii), _p(dL_dout),
+                _p(g["means2D"]), _p(g["normal"]), _p(g["opacity"]), _p(g["means3D"]),
+                _p(g["transMat"]), _p(g["scales"]), _p(g["rotations"]))
+        if rc != 0:
+            raise RuntimeError("reference backward failed")
+        return g
+
+    def state(self, name):
+        ptr, cnt = ctypes.c_void_p(), ctypes.c_size_t()
+        rc = self.lib.ref_dssr_state(self.h, name.encode(), ctypes.byref(ptr), ctypes.byref(cnt))
+        if rc != 0:
+            raise RuntimeError(f"ref_dssr_state({name}) -> {rc}")
+        out = torch.empty(cnt.value, dtype=_STATE_DTYPES[name], device="cuda")
+        if cnt.value:
+            torch.cuda.synchronize()
+            rc = torch.cuda.cudart().cudaMemcpy(out.data_ptr(), ptr.value,
+                                                cnt.value * out.element_size(), 3)
+            if int(rc) != 0:
+                raise RuntimeError(f"cudaMemcpy failed: {rc}")
+        return out.cpu()
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    P = means3D.shape[0]
+    present = torch.zeros(P, dtype=torch.bool, device=means3D.device)
+    torch.cuda.synchronize()
+    rc = _load().ref_dssr_mark_visible(P, _p(means3D), _p(viewmatrix), _p(projmatrix),
+                                       _p(present))
+    if rc != 0:
+        raise RuntimeError("reference mark_visible failed")
+    return present
+
+
+def dist2(points, sync=True):
+    P = points.shape[0]
+    out = torch.empty(P, dtype=torch.float32, device=points.device)
+    torch.cuda.synchronize()
+    fn = _load().ref_sknn_dist2 if sync else _load().ref_sknn_dist2_nosync
+    rc = fn(P, _p(points), _p(out))
+    if rc != 0:
+        raise RuntimeError("reference distCUDA2 failed")
+    return out

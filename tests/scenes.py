@@ -1,0 +1,171 @@
+"""Seeded synthetic inputs for the rasterizer and the kNN.
+
+numpy only (Generator(PCG64) streams are identical on every machine), float32 outputs.
+Used by the tests, by bench.py and by the golden-fixture generator.
+"""
+import math
+
+import numpy as np
+
+CONFIGS = {
+    # name: (H, W, vfov_deg, P, keyframes)
+    "C0": (16, 256, 30.0, 2000, 1),        # tiny: CPU-oracle sized
+    "C1": (16, 1024, 30.0, 20000, 1),
+    "C2": (64, 1024, 33.2, 500000, 1),
+    "C3": (64, 2048, 26.9, 1000000, 8),
+    "C4": (128, 2048, 45.0, 2000000, 32),
+}
+
+
+def intrinsics(H, W, vfov_deg):
+    """K as in DSSR/tests/generate_input.py:27-47; projmatrix = eye(4) with [:3,:3]=K^T
+    (scene/cameras.py:48-50)."""
+    vfov = math.radians(vfov_deg)
+    K = np.array([[-W / (2 * math.pi), 0, W * 0.5], [0, -H / vfov, H * 0.5], [0, 0, 1]],
+                 dtype=np.float64)
+    proj = np.eye(4)
+    proj[:3, :3] = K.T
+    return proj.astype(np.float32)
+
+
+def pose(k):
+    """world_T_lidar of keyframe k: 0.5 m steps along x, 2 degrees of yaw per step."""
+    yaw = math.radians(2.0 * k)
+    T = np.eye(4)
+    T[:3, :3] = [[math.cos(yaw), -math.sin(yaw), 0], [math.sin(yaw), math.cos(yaw), 0], [0, 0, 1]]
+    T[:3, 3] = [0.5 * k, 0, 0]
+    return T
+
+
+def viewmatrix(k=0):
+    """inv(world_T_lidar) transposed (scene/cameras.py:43-46)."""
+    return np.linalg.inv(pose(k)).T.astype(np.float32)
+
+
+def _rotmat_to_quat(R):
+    """(w,x,y,z) of a batch of rotation matrices [n,3,3] (Shepperd's method)."""
+    n = R.shape[0]
+    q = np.empty((n, 4))
+    tr = R[:, 0, 0] + R[:, 1, 1] + R[:, 2, 2]
+    c0 = tr > 0
+    c1 = (~c0) & (R[:, 0, 0] >= R[:, 1, 1]) & (R[:, 0, 0] >= R[:, 2, 2])
+    c2 = (~c0) & (~c1) & (R[:, 1, 1] >= R[:, 2, 2])
+    c3 = ~(c0 | c1 | c2)
+    s = np.sqrt(np.maximum(tr[c0] + 1.0, 1e-12)) * 2
+    q[c0] = np.stack([0.25 * s, (R[c0, 2, 1] - R[c0, 1, 2]) / s, (R[c0, 0, 2] - R[c0, 2, 0]) / s,
+                      (R[c0, 1, 0] - R[c0, 0, 1]) / s], 1)
+    s = np.sqrt(np.maximum(1.0 + R[c1, 0, 0] - R[c1, 1, 1] - R[c1, 2, 2], 1e-12)) * 2
+    q[c1] = np.stack([(R[c1, 2, 1] - R[c1, 1, 2]) / s, 0.25 * s, (R[c1, 0, 1] + R[c1, 1, 0]) / s,
+                      (R[c1, 0, 2] + R[c1, 2, 0]) / s], 1)
+    s = np.sqrt(np.maximum(1.0 + R[c2, 1, 1] - R[c2, 0, 0] - R[c2, 2, 2], 1e-12)) * 2
+    q[c2] = np.stack([(R[c2, 0, 2] - R[c2, 2, 0]) / s, (R[c2, 0, 1] + R[c2, 1, 0]) / s, 0.25 * s,
+                      (R[c2, 1, 2] + R[c2, 2, 1]) / s], 1)
+    s = np.sqrt(np.maximum(1.0 + R[c3, 2, 2] - R[c3, 0, 0] - R[c3, 1, 1], 1e-12)) * 2
+    q[c3] = np.stack([(R[c3, 1, 0] - R[c3, 0, 1]) / s, (R[c3, 0, 2] + R[c3, 2, 0]) / s,
+                      (R[c3, 1, 2] + R[c3, 2, 1]) / s, 0.25 * s], 1)
+    return q / np.linalg.norm(q, axis=1, keepdims=True)
+
+
+def surfels(P, H, W, vfov_deg, seed=0):
+    """Random surfel cloud around the sensor; returns dict of float32 arrays."""
+    rng = np.random.default_rng(seed)
+    vfov = math.radians(vfov_deg)
+    az = rng.uniform(-math.pi, math.pi, P)
+    el = rng.uniform(-vfov / 2, vfov / 2, P)
+    out = rng.random(P) < 0.10                      # 10 %: up to 5 deg outside the band
+    el[out] = np.sign(el[out]) * (vfov / 2 + rng.uniform(0, math.radians(5.0), out.sum()))
+    r = np.exp(rng.uniform(math.log(3.0), math.log(60.0), P))
+    u = rng.random(P)
+    near, far = u < 0.005, (u >= 0.005) & (u < 0.01)  # 1 %: outside (0.1, 120]
+    r[near] = rng.uniform(0.05, 0.1, near.sum())
+    r[far] = rng.uniform(120.0, 130.0, far.sum())
+    d = np.stack([np.cos(az) * np.cos(el), np.sin(az) * np.cos(el), np.sin(el)], 1)
+    means = d * r[:, None]
+    # normal = -dir rotated by a random axis-angle of at most 60 deg; 5 % flipped
+    axis = rng.normal(size=(P, 3))
+    axis -= (axis * d).sum(1, keepdims=True) * d
+    axis /= np.linalg.norm(axis, axis=1, keepdims=True)
+    ang = rng.uniform(0, math.radians(60.0), P)
+    nrm = -d * np.cos(ang)[:, None] + np.cross(axis, -d) * np.sin(ang)[:, None]
+    flip = rng.random(P) < 0.05
+    nrm[flip] *= -1
+    # frame with third axis = normal, random in-plane rotation
+    t = np.cross(nrm, axis)
+    t /= np.linalg.norm(t, axis=1, keepdims=True)
+    b = np.cross(nrm, t)
+    phi = rng.uniform(0, 2 * math.pi, P)
+    e0 = t * np.cos(phi)[:, None] + b * np.sin(phi)[:, None]
+    e1 = np.cross(nrm, e0)
+    R = np.stack([e0, e1, nrm], 2)                   # columns
+    quat = _rotmat_to_quat(R)
+    pix = 2 * math.pi / W
+    scales = np.clip(r[:, None] * pix * rng.uniform(0.5, 2.0, (P, 2)), 0.02, 0.3)
+    opa = rng.uniform(0.3, 0.99, P)
+    opa[rng.random(P) < 0.02] = 1.0
+    return {
+        "means3D": means.astype(np.float32),
+        "scales": scales.astype(np.float32),
+        "rotations": quat.astype(np.float32),
+        "opacities": opa.astype(np.float32)[:, None],
+    }
+
+
+def upstream_grad(H, W, seed=1):
+    return np.random.default_rng(seed).normal(size=(7, H, W)).astype(np.float32)
+
+
+def make_scene(name_or_dims, seed=0, keyframe=0, P=None):
+    """Full input set for one frame: surfels + matrices + dL_dout."""
+    if isinstance(name_or_dims, str):
+        H, W, vfov, P0, _ = CONFIGS[name_or_dims]
+    else:
+        H, W, vfov, P0 = name_or_dims
+    P = P0 if P is None else P
+    s = surfels(P, H, W, vfov, seed)
+    s.update(H=H, W=W, viewmatrix=viewmatrix(keyframe), projmatrix=intrinsics(H, W, vfov),
+             dL_dout=upstream_grad(H, W, seed + 1))
+    return s
+
+
+def reference_test_scene():
+    """The one fixture the reference ships: DSSR/tests/generate_input.py:5-68 — a 32x32
+    grid of surfels on the z=0 plane, 2048x512 image, hfov 2*pi, vfov pi/2."""
+    n, length = 32, 10.0
+    x = np.linspace(-1, 1, n) * length
+    xx, yy = np.meshgrid(x, x)
+    means = np.stack([xx, yy, np.zeros_like(xx)], -1).reshape(-1, 3)
+    P = means.shape[0]
+    quat = np.zeros((P, 4)); quat[:, 0] = 1.0
+    scales = np.full((P, 2), length / (n - 1))
+    opa = np.ones((P, 1))
+    W, H = 2048, 512
+    hfov, vfov = 2 * math.pi, math.pi / 2
+    K = np.array([[-W / hfov, 0, W * 0.5], [0, -H / vfov, H * 0.5], [0, 0, 1]], dtype=np.float32)
+    proj = np.zeros((4, 4), dtype=np.float32)
+    proj[:3, :3] = K
+    proj = proj.T.copy()
+    world_T_lidar = np.array([[0, -1, 0, 0], [0, 0, 1, 0.49], [-1, 0, 0, 5], [0, 0, 0, 1]],
+                             dtype=np.float32)
+    view = np.linalg.inv(world_T_lidar).T.astype(np.float32).copy()
+    return {"means3D": means.astype(np.float32), "scales": scales.astype(np.float32),
+            "rotations": quat.astype(np.float32), "opacities": opa.astype(np.float32),
+            "H": H, "W": W, "viewmatrix": view, "projmatrix": proj,
+            "dL_dout": upstream_grad(H, W, 1)}
+
+
+def knn_cloud(P, seed=0, keyframes=64):
+    """Accumulated cloud for distCUDA2: `keyframes` scans from the range model above, in
+    the world frame, plus 0.1 % exact duplicates."""
+    per = (P + keyframes - 1) // keyframes
+    rng = np.random.default_rng(seed)
+    chunks = []
+    for k in range(keyframes):
+        s = surfels(per, 64, 1024, 33.2, seed=seed * 1000 + k + 1)["means3D"].astype(np.float64)
+        T = pose(k)
+        chunks.append(s @ T[:3, :3].T + T[:3, 3])
+    pts = np.concatenate(chunks)[:P]
+    ndup = max(1, P // 1000)
+    src = rng.integers(0, P, ndup)
+    dst = rng.integers(0, P, ndup)
+    pts[dst] = pts[src]
+    return pts.astype(np.float32)
