@@ -152,9 +152,6 @@ def debug_state(geomBuffer, binningBuffer, imageBuffer, name):
         n = cnt.value
         out = torch.empty(n, dtype=dtype, device=dev)
         if n:
-            cudart = torch.cuda.cudart()
             torch.cuda.synchronize()
-            rc = cudart.cudaMemcpy(out.data_ptr(), ptr.value, n * out.element_size(), 3)
-            if int(rc) != 0:
-                raise RuntimeError(f"cudaMemcpy failed: {rc}")
+            _n.copy_from_device_ptr(out, ptr.value, n * out.element_size())
         return out.cpu()

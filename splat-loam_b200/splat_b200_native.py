@@ -108,3 +108,26 @@ def last_error():
 def check(rc):
     if rc != 0:
         raise RuntimeError(last_error())
+
+
+_cudart = None
+
+
+def copy_from_device_ptr(dst_tensor, src_ptr, nbytes):
+    """cudaMemcpy(device -> device) from a raw pointer into a torch tensor (debug only)."""
+    global _cudart
+    if _cudart is None:
+        for name in ("libcudart.so.12", "libcudart.so"):
+            try:
+                _cudart = ctypes.CDLL(name)
+                break
+            except OSError:
+                continue
+        if _cudart is None:
+            raise RuntimeError("libcudart not found")
+        _cudart.cudaMemcpy.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t,
+                                       ctypes.c_int]
+        _cudart.cudaMemcpy.restype = ctypes.c_int
+    rc = _cudart.cudaMemcpy(dst_tensor.data_ptr(), src_ptr, nbytes, 3)
+    if rc != 0:
+        raise RuntimeError(f"cudaMemcpy failed with {rc}")

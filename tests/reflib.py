@@ -25,6 +25,24 @@ def available():
 
 
 _lib = None
+_cudart = None
+
+
+def _copy(dst, src_ptr, nbytes):
+    global _cudart
+    if _cudart is None:
+        for name in ("libcudart.so.12", "libcudart.so"):
+            try:
+                _cudart = ctypes.CDLL(name)
+                break
+            except OSError:
+                continue
+        _cudart.cudaMemcpy.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t,
+                                       ctypes.c_int]
+        _cudart.cudaMemcpy.restype = ctypes.c_int
+    rc = _cudart.cudaMemcpy(dst.data_ptr(), src_ptr, nbytes, 3)
+    if rc != 0:
+        raise RuntimeError(f"cudaMemcpy failed with {rc}")
 
 
 def _load():
@@ -117,10 +135,7 @@ class RefRasterizer:
         out = torch.empty(cnt.value, dtype=_STATE_DTYPES[name], device="cuda")
         if cnt.value:
             torch.cuda.synchronize()
-            rc = torch.cuda.cudart().cudaMemcpy(out.data_ptr(), ptr.value,
-                                                cnt.value * out.element_size(), 3)
-            if int(rc) != 0:
-                raise RuntimeError(f"cudaMemcpy failed: {rc}")
+            _copy(out, ptr.value, cnt.value * out.element_size())
         return out.cpu()
 
 
