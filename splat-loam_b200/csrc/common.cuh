@@ -34,6 +34,7 @@
 #define SORT_BLOCK_ELEMS (SORT_THREADS * SORT_ITEMS)   // 4096
 #define SORT_MAX_BINS 1024
 #define SORT_MAX_PASSES 6
+#define HIST_REPL 32              // replicas of the global digit histograms
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
@@ -136,7 +137,7 @@ struct BinLayout {
     if (keep_unsorted) o = align_up(o + C * 8, 256);
     // [hist | tickets | status] are zeroed with ONE memset per forward
     hist = o;
-    hist_bytes = (size_t)SORT_MAX_PASSES * SORT_MAX_BINS * 4;
+    hist_bytes = (size_t)HIST_REPL * SORT_MAX_PASSES * SORT_MAX_BINS * 4;
     o = align_up(o + hist_bytes, 256);
     tickets = o;    o = align_up(o + SORT_MAX_PASSES * 4, 256);
     status = o;
@@ -257,7 +258,7 @@ void launch_emit(const FwdParams &p, const GeomView &g, const ImageView &im,
 void launch_sort(const GeomView &g, const ImageView &im, const BinView &b,
                  const SortPlan &sp, uint32_t capacity, cudaStream_t s);
 void launch_digit_scan(const uint32_t *hist, uint32_t *digit_base, int npass, uint2 *ranges,
-                       int tiles, int tile_pass_single, cudaStream_t s);
+                       int tiles, int tile_pass_single, int nrepl, cudaStream_t s);
 unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long *b,
                                        unsigned long long *keys_out, uint32_t *plist_out,
                                        const uint32_t *num_ptr, uint32_t capacity,

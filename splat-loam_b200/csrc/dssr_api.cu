@@ -3,7 +3,9 @@
 // CudaRasterizer::Rasterizer::forward / backward / markVisible
 // (submodules/diff-surfel-spherical-rasterization/cuda_rasterizer/rasterizer_impl.cu:
 // 117-122, 170-262, 266-313).
+#include <chrono>
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 
@@ -36,6 +38,20 @@ thread_local cudaEvent_t g_event = nullptr;
       return fail("[CUDA ERROR] in %s: %s", what, cudaGetErrorString(e_));    \
   } while (0)
 
+// SPLAT_B200_TRACE=1: host-side time of each phase of dssr_forward on stderr
+struct Trace {
+  bool on;
+  std::chrono::steady_clock::time_point t;
+  Trace() : on(getenv("SPLAT_B200_TRACE") != nullptr), t(std::chrono::steady_clock::now()) {}
+  void lap(const char *what) {
+    if (!on) return;
+    auto n = std::chrono::steady_clock::now();
+    fprintf(stderr, "[splat trace] %-22s %8.1f us\n", what,
+            std::chrono::duration<double, std::micro>(n - t).count());
+    t = n;
+  }
+};
+
 int ensure_host_scratch() {
   if (!g_pinned) CUDA_TRY(cudaHostAlloc((void **)&g_pinned, 64, cudaHostAllocPortable));
   if (!g_event) CUDA_TRY(cudaEventCreateWithFlags(&g_event, cudaEventDisableTiming));
@@ -51,12 +67,6 @@ int run_binning_and_render(const dssr_forward_args *a, const FwdParams &fp,
   char *bptr = a->binning_alloc(a->binning_ctx, bl.total);
   if (!bptr) return fail("binning_alloc(%zu) returned NULL", bl.total);
   BinView bv = make_bin_view(bptr, capacity, keep, sp);
-  BinHeader bh;
-  memset(&bh, 0, sizeof bh);
-  bh.magic = 0x42494e31u;
-  bh.capacity = capacity;
-  bh.keep_unsorted = keep;
-  CUDA_TRY(cudaMemcpyAsync(bv.hdr, &bh, sizeof bh, cudaMemcpyHostToDevice, st));
   CUDA_TRY(cudaMemsetAsync(bv.hist, 0, bv.zero_bytes, st));
   launch_emit(fp, gv, iv, bv, sp, capacity, st);
   LAUNCH_CHECK(dbg, st, "emit");
@@ -110,6 +120,10 @@ int dssr_forward(const dssr_forward_args *a, int *num_rendered) {
     return fail("dssr_forward: need scales+rotations or transMat_precomp");
   if (!a->geom_alloc || !a->binning_alloc || !a->image_alloc)
     return fail("dssr_forward: NULL allocator callback");
+  if (((uintptr_t)a->scales & 7) || ((uintptr_t)a->rotations & 15) ||
+      ((uintptr_t)a->transMat_precomp & 15))
+    return fail("dssr_forward: scales must be 8-byte and rotations / transMat_precomp 16-byte aligned");
+  Trace tr;
   if (ensure_host_scratch()) return 1;
   const bool dbg = a->debug & 1;
 
@@ -124,6 +138,7 @@ int dssr_forward(const dssr_forward_args *a, int *num_rendered) {
   if (!iptr) return fail("image_alloc(%zu) returned NULL", il.total);
   GeomView gv = make_geom_view(gptr, a->P);
   ImageView iv = make_image_view(iptr, a->W, a->H);
+  tr.lap("alloc geom+image");
 
   FwdParams fp;
   fp.P = a->P; fp.W = a->W; fp.H = a->H;
@@ -135,17 +150,13 @@ int dssr_forward(const dssr_forward_args *a, int *num_rendered) {
   fp.viewmatrix = a->viewmatrix; fp.projmatrix = a->projmatrix;
   fp.out_maps = a->out_maps; fp.radii = a->radii;
 
-  GeomHeader gh;
-  memset(&gh, 0, sizeof gh);
-  gh.magic = 0x47454f31u;
-  gh.P = a->P; gh.W = a->W; gh.H = a->H;
-  CUDA_TRY(cudaMemcpyAsync(gv.hdr, &gh, sizeof gh, cudaMemcpyHostToDevice, st));
   launch_preprocess(fp, gv, iv, st);
   LAUNCH_CHECK(dbg, st, "preprocess");
   launch_chunk_scan(gv, st);
   LAUNCH_CHECK(dbg, st, "chunk_scan");
   CUDA_TRY(cudaMemcpyAsync(g_pinned, &gv.hdr->num_rendered, 8, cudaMemcpyDeviceToHost, st));
   CUDA_TRY(cudaEventRecord(g_event, st));
+  tr.lap("enqueue preprocess");
 
   // With a capacity hint the rest of the frame is enqueued BEFORE the host waits for
   // the instance count (the reference blocks here: rasterizer_impl.cu:216-219).
@@ -153,13 +164,16 @@ int dssr_forward(const dssr_forward_args *a, int *num_rendered) {
   if (hint > 0x3fffffff) hint = 0x3fffffff;
   if (hint > 0)
     if (run_binning_and_render(a, fp, gv, iv, sp, (uint32_t)hint, st)) return 1;
+  tr.lap("enqueue binning (hint)");
   CUDA_TRY(cudaEventSynchronize(g_event));
+  tr.lap("wait for count");
   const uint32_t N = g_pinned[0], status = g_pinned[1];
   if (status & 1u)
     return fail("Point is filtered although prefiltered is set. This shouldn't happen!");
   if (N > 0x3fffffffu) return fail("dssr_forward: %u instances exceed the 2^30 limit", N);
   if (hint <= 0 || (int64_t)N > hint)
     if (run_binning_and_render(a, fp, gv, iv, sp, N, st)) return 1;
+  tr.lap("enqueue binning (exact)");
   *num_rendered = (int)N;
   return 0;
 }
@@ -176,6 +190,11 @@ int dssr_backward(const dssr_backward_args *a) {
   if (!a->geom_buffer || !a->binning_buffer || !a->image_buffer || !a->dL_dout ||
       !a->radii || !a->viewmatrix || !a->projmatrix)
     return fail("dssr_backward: NULL input pointer");
+  if (((uintptr_t)a->scales & 7) || ((uintptr_t)a->rotations & 15) ||
+      ((uintptr_t)a->dL_dscales & 7) || ((uintptr_t)a->dL_drotations & 15) ||
+      ((uintptr_t)a->dL_dtransMat & 15))
+    return fail("dssr_backward: scales / dL_dscales must be 8-byte and rotations / "
+                "dL_drotations / dL_dtransMat 16-byte aligned");
   const bool dbg = a->debug & 1;
   CUDA_TRY(cudaMemsetAsync(a->dL_dmeans2D, 0, 12 * P, st));
   CUDA_TRY(cudaMemsetAsync(a->dL_dnormal, 0, 12 * P, st));

@@ -29,7 +29,8 @@ render_forward_kernel(const uint2 *__restrict__ ranges,
                       const uint32_t *__restrict__ point_list,
                       const float4 *__restrict__ rec, const float4 *__restrict__ cull,
                       const float *__restrict__ projmatrix, int W, int H, int tiles_x,
-                      uint32_t capacity, float *__restrict__ final_T, uint32_t *__restrict__ n_contrib,
+                      uint32_t capacity, uint32_t P, float *__restrict__ final_T,
+                      uint32_t *__restrict__ n_contrib,
                       float *__restrict__ out) {
   __shared__ float4 s_rec[FW_WARPS][32][4];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -59,10 +60,13 @@ render_forward_kernel(const uint2 *__restrict__ ranges,
   // software prefetch of the next 32 entries
   uint32_t nid = 0;
   float4 ncb = make_float4(0.f, 0.f, 0.f, 0.f);
+  // (id < P only fails on the garbage a too-small capacity hint leaves behind; that
+  // frame is re-run with the exact size)
   bool nhave = range.x + lane < range.y;
   if (nhave) {
     nid = point_list[range.x + lane];
-    ncb = cull[nid];
+    nhave = nid < P;
+    if (nhave) ncb = cull[nid];
   }
   for (uint32_t base = range.x; base < range.y; base += 32) {
     if (__all_sync(0xffffffffu, done)) break;
@@ -74,7 +78,8 @@ render_forward_kernel(const uint2 *__restrict__ ranges,
       nhave = ni < range.y;
       if (nhave) {
         nid = point_list[ni];
-        ncb = cull[nid];
+        nhave = nid < P;
+        if (nhave) ncb = cull[nid];
       }
     }
     const bool hit = have && (!cull_on || cull_overlap(cb, bx0, bx1, by0, by1, inv_period));
@@ -156,5 +161,5 @@ void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageVie
   dim3 grid(im.tiles_x, (p.H + 2 * SUB_H - 1) / (2 * SUB_H));
   render_forward_kernel<<<grid, FW_WARPS * 32, 0, s>>>(
       im.ranges, b.point_list, g.rec, g.cull, p.projmatrix, p.W, p.H, im.tiles_x,
-      capacity, im.final_T, im.n_contrib, p.out_maps);
+      capacity, (uint32_t)p.P, im.final_T, im.n_contrib, p.out_maps);
 }

@@ -41,10 +41,13 @@ __device__ __forceinline__ void st_volatile_u32(uint32_t *p, uint32_t v) {
 // reference's memset + identifyTileRanges leaves).
 __global__ void __launch_bounds__(SORT_MAX_BINS)
 digit_scan_kernel(const uint32_t *__restrict__ hist, uint32_t *__restrict__ digit_base,
-                  uint2 *ranges, int tiles, int tile_pass_single) {
+                  uint2 *ranges, int tiles, int tile_pass_single, int nrepl) {
   __shared__ uint32_t s_warp[32];
   const int pass = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  uint32_t v = hist[pass * SORT_MAX_BINS + tid];
+  uint32_t v = 0;
+#pragma unroll 8
+  for (int r = 0; r < nrepl; r++)
+    v += hist[(size_t)r * (SORT_MAX_PASSES * SORT_MAX_BINS) + pass * SORT_MAX_BINS + tid];
   uint32_t inc = v;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -199,9 +202,9 @@ sort_pass_kernel(const unsigned long long *__restrict__ in, unsigned long long *
 }  // namespace
 
 void launch_digit_scan(const uint32_t *hist, uint32_t *digit_base, int npass, uint2 *ranges,
-                       int tiles, int tile_pass_single, cudaStream_t s) {
+                       int tiles, int tile_pass_single, int nrepl, cudaStream_t s) {
   digit_scan_kernel<<<npass, SORT_MAX_BINS, 0, s>>>(hist, digit_base, ranges, tiles,
-                                                    tile_pass_single);
+                                                    tile_pass_single, nrepl);
 }
 
 // Runs `npass` passes ping-ponging between a and b (pass 0 reads a).  When
@@ -233,7 +236,7 @@ unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long
 void launch_sort(const GeomView &g, const ImageView &im, const BinView &b,
                  const SortPlan &sp, uint32_t capacity, cudaStream_t s) {
   const int single = (sp.npass == 4) ? 3 : -1;
-  launch_digit_scan(b.hist, b.digit_base, sp.npass, im.ranges, im.tiles, single, s);
+  launch_digit_scan(b.hist, b.digit_base, sp.npass, im.ranges, im.tiles, single, HIST_REPL, s);
   launch_sort_passes(b.words_a, b.words_b, b.keys, b.point_list, &g.hdr->num_rendered,
                      capacity, b.status, b.status_off, b.tickets, b.digit_base, sp.npass,
                      sp.shift, sp.bits, 1, sp.idx_bits, b.nblk, s);

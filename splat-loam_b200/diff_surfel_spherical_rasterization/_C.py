@@ -36,18 +36,31 @@ def _ptr(t):
     return t.data_ptr() if t.numel() else None
 
 
-class _Grower:
-    """Allocator callback state: one growable uint8 tensor (resizeFunctional,
-    rasterize_points.cu:24-30)."""
+# Allocator callbacks (resizeFunctional, rasterize_points.cu:24-30).  ONE module-level
+# C callback; `ctx` is a key into _slots.  (A per-call bound-method callback would form a
+# reference cycle and keep the buffers alive until the cyclic GC runs, which forces the
+# caching allocator to cudaMalloc on every frame.)
+_slots = {}
+_next_slot = [1]
 
-    def __init__(self, device):
-        self.tensor = torch.empty(0, dtype=torch.uint8, device=device)
-        self.cb = _n.ALLOC_FN(self._alloc)
 
-    def _alloc(self, _ctx, nbytes):
-        if self.tensor.numel() < nbytes:
-            self.tensor = torch.empty(int(nbytes), dtype=torch.uint8, device=self.tensor.device)
-        return self.tensor.data_ptr()
+def _alloc(ctx, nbytes):
+    slot = _slots[ctx]
+    t = slot[0]
+    if t.numel() < nbytes:
+        t = torch.empty(int(nbytes), dtype=torch.uint8, device=t.device)
+        slot[0] = t
+    return t.data_ptr()
+
+
+_ALLOC_CB = _n.ALLOC_FN(_alloc)
+
+
+def _new_slot(device):
+    key = _next_slot[0]
+    _next_slot[0] = key + 1 if key < (1 << 40) else 1
+    _slots[key] = [torch.empty(0, dtype=torch.uint8, device=device)]
+    return key
 
 
 def rasterize_gaussians(means3D, opacity, scales, rotations, scale_modifier, transMat_precomp,
@@ -63,7 +76,7 @@ def rasterize_gaussians(means3D, opacity, scales, rotations, scale_modifier, tra
     with torch.cuda.device(dev):
         out = torch.empty((7, H, W), dtype=torch.float32, device=dev)
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
-        geom, binning, img = _Grower(dev), _Grower(dev), _Grower(dev)
+        kg, kb, ki = _new_slot(dev), _new_slot(dev), _new_slot(dev)
         means3D_c, opacity_c = _f32(means3D), _f32(opacity)
         scales_c, rot_c, pre_c = _f32(scales), _f32(rotations), _f32(transMat_precomp)
         view_c, proj_c = _f32(viewmatrix), _f32(projmatrix)
@@ -73,13 +86,17 @@ def rasterize_gaussians(means3D, opacity, scales, rotations, scale_modifier, tra
             P, W, H, float(scale_modifier), int(bool(prefiltered)), int(bool(debug)),
             _ptr(means3D_c), _ptr(opacity_c), _ptr(scales_c), _ptr(rot_c), _ptr(pre_c),
             _ptr(view_c), _ptr(proj_c), _ptr(out), _ptr(radii),
-            geom.cb, None, binning.cb, None, img.cb, None, hint,
+            _ALLOC_CB, kg, _ALLOC_CB, kb, _ALLOC_CB, ki, hint,
             torch.cuda.current_stream(dev).cuda_stream)
         n = ctypes.c_int(0)
-        _n.check(_lib.dssr_forward(ctypes.byref(a), ctypes.byref(n)))
+        try:
+            rc = _lib.dssr_forward(ctypes.byref(a), ctypes.byref(n))
+        finally:
+            geom, binning, img = _slots.pop(kg)[0], _slots.pop(kb)[0], _slots.pop(ki)[0]
+        _n.check(rc)
         if _USE_HINT:
             _hints[key] = int(n.value * 1.25) + 4096
-    return n.value, out, radii, geom.tensor, binning.tensor, img.tensor
+    return n.value, out, radii, geom, binning, img
 
 
 def rasterize_gaussians_backward(means3D, radii, scales, rotations, scale_modifier,
@@ -97,12 +114,13 @@ def rasterize_gaussians_backward(means3D, radii, scales, rotations, scale_modifi
     with torch.cuda.device(dev):
         # one allocation, seven contiguous slices (the reference does seven torch::zeros,
         # rasterize_points.cu:116-122; the kernels here write every element themselves)
-        flat = torch.empty(28 * P, dtype=torch.float32, device=dev)
         cuts = (3, 3, 3, 1, 12, 2, 4)
-        views, o = [], 0
-        for c in cuts:
-            views.append(flat[o:o + c * P].view(P, c))
-            o += c * P
+        starts, o = [], 0
+        for c in cuts:           # every slice starts 256-byte aligned (float4 accesses)
+            starts.append(o)
+            o += (c * P + 63) // 64 * 64
+        flat = torch.empty(o, dtype=torch.float32, device=dev)
+        views = [flat[b:b + c * P].view(P, c) for b, c in zip(starts, cuts)]
         dmeans3D, dmeans2D, dnormal, dopacity, dtrans, dscales, drot = views
         if P:
             means3D_c, scales_c, rot_c = _f32(means3D), _f32(scales), _f32(rotations)

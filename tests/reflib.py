@@ -96,6 +96,11 @@ class RefRasterizer:
 
     def forward(self, means3D, opacities, scales, rotations, viewmatrix, projmatrix, H, W,
                 scale_modifier=1.0, precomp=None, prefiltered=False, sync=True):
+        means3D, opacities, viewmatrix, projmatrix = (
+            t.contiguous() for t in (means3D, opacities, viewmatrix, projmatrix))
+        scales = scales.contiguous() if scales is not None else None
+        rotations = rotations.contiguous() if rotations is not None else None
+        precomp = precomp.contiguous() if precomp is not None else None
         P = means3D.shape[0]
         self.P, self.H, self.W = P, H, W
         dev = means3D.device

@@ -25,7 +25,7 @@ def intrinsics(H, W, vfov_deg):
                  dtype=np.float64)
     proj = np.eye(4)
     proj[:3, :3] = K.T
-    return proj.astype(np.float32)
+    return np.ascontiguousarray(proj, dtype=np.float32)
 
 
 def pose(k):
@@ -39,7 +39,7 @@ def pose(k):
 
 def viewmatrix(k=0):
     """inv(world_T_lidar) transposed (scene/cameras.py:43-46)."""
-    return np.linalg.inv(pose(k)).T.astype(np.float32)
+    return np.ascontiguousarray(np.linalg.inv(pose(k)).T, dtype=np.float32)
 
 
 def _rotmat_to_quat(R):
@@ -169,3 +169,67 @@ def knn_cloud(P, seed=0, keyframes=64):
     dst = rng.integers(0, P, ndup)
     pts[dst] = pts[src]
     return pts.astype(np.float32)
+
+
+def edge_scene():
+    """Hand-made edge cases on a 40x200 image (neither a multiple of
+    16): azimuth-seam straddlers, elevation beyond the image, back-facing, range <= 0.1 and
+    > 120, a giant near surfel whose tile rect is wider than the grid (duplicate tiles),
+    opacity 1.0 (0.99 clamp), stacked opaque surfels (mid-list termination), tiny opacity."""
+    H, W, vfov = 40, 200, 60.0
+    rng = np.random.default_rng(7)
+    rows = []   # (az, el, r, tilt_deg, sx, sy, opa, flip)
+
+    def add(az, el, r, tilt=0.0, sx=0.05, sy=0.05, opa=0.8, flip=False):
+        rows.append((az, el, r, tilt, sx, sy, opa, flip))
+
+    for a in (math.pi - 0.003, -math.pi + 0.004, math.pi - 0.02, -math.pi + 0.015):
+        add(a, 0.05, 6.0, 20.0, 0.12, 0.06)                      # straddle the +-pi seam
+    add(0.3, math.radians(40.0), 5.0)                            # above the image
+    add(0.3, math.radians(-33.0), 5.0, sx=0.3, sy=0.3)           # partly below
+    add(1.0, 0.0, 5.0, flip=True)                                # back-facing
+    add(1.2, 0.0, 0.08); add(1.3, 0.0, 0.1); add(1.4, 0.0, 125.0); add(1.5, 0.0, 120.0)
+    add(-2.0, 0.0, 0.6, 10.0, 1.5, 1.2, 0.6)                     # giant: rect wider than grid
+    add(2.0, 0.1, 4.0, 0.0, 0.2, 0.2, 1.0)                       # alpha clamp 0.99
+    for k in range(12):                                           # opaque stack -> termination
+        add(-1.0, -0.1, 3.0 + 0.25 * k, 5.0 * k, 0.25, 0.25, 0.97)
+    add(-1.0, -0.1, 8.0, 0.0, 0.4, 0.4, 0.9)                     # behind the stack
+    add(0.7, 0.2, 7.0, 0.0, 0.1, 0.1, 0.003)                     # below 1/255
+    add(0.75, 0.2, 7.0, 0.0, 0.1, 0.1, 1.0 / 255.0)
+    add(-0.5, 0.3, 9.0, 75.0, 0.3, 0.02, 0.9)                    # grazing, very anisotropic
+    for _ in range(40):                                           # filler
+        add(rng.uniform(-math.pi, math.pi), rng.uniform(-0.5, 0.5), rng.uniform(2, 30),
+            rng.uniform(0, 70), rng.uniform(0.02, 0.4), rng.uniform(0.02, 0.4),
+            rng.uniform(0.2, 1.0))
+    a = np.array([r[:7] for r in rows], dtype=np.float64)
+    flip = np.array([r[7] for r in rows])
+    az, el, r, tilt = a[:, 0], a[:, 1], a[:, 2], np.radians(a[:, 3])
+    d = np.stack([np.cos(az) * np.cos(el), np.sin(az) * np.cos(el), np.sin(el)], 1)
+    axis = np.cross(d, np.array([0.0, 0.0, 1.0]) + 0.1 * d[:, ::-1])
+    axis /= np.linalg.norm(axis, axis=1, keepdims=True)
+    nrm = -d * np.cos(tilt)[:, None] + np.cross(axis, -d) * np.sin(tilt)[:, None]
+    nrm[flip] *= -1
+    t = np.cross(nrm, axis); t /= np.linalg.norm(t, axis=1, keepdims=True)
+    R = np.stack([t, np.cross(nrm, t), nrm], 2)
+    s = {"means3D": (d * r[:, None]).astype(np.float32), "scales": a[:, 4:6].astype(np.float32),
+         "rotations": _rotmat_to_quat(R).astype(np.float32),
+         "opacities": a[:, 6:7].astype(np.float32), "H": H, "W": W,
+         "viewmatrix": viewmatrix(1), "projmatrix": intrinsics(H, W, vfov),
+         "dL_dout": upstream_grad(H, W, 3)}
+    # the scene is defined in the frame of keyframe 0, viewed from keyframe 1
+    return s
+
+
+def precomp_scene():
+    """Inputs for the transMat_precomp path: the T matrices of scene C0 as the reference
+    computes them are fed back as `cov3D_precomp` (filled in by the caller)."""
+    return make_scene("C0", seed=5)
+
+
+def input_digest(s):
+    """Stable digest of a scene's arrays, stored in golden files to detect generator drift."""
+    import hashlib
+    h = hashlib.sha256()
+    for k in ("means3D", "scales", "rotations", "opacities", "viewmatrix", "projmatrix", "dL_dout"):
+        h.update(np.ascontiguousarray(s[k]).tobytes())
+    return h.hexdigest()
