@@ -1,0 +1,395 @@
+#!/usr/bin/env python
+"""bench.py — surfel raster fwd+bwd frames/s (BASELINE.json metric) on N GPUs of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config C2]
+
+A "step" is one pass of the hot path over one synthetic frame: rasterizer forward +
+backward through the reference-facing `_C` calls (which go through the C-ABI of
+libsplat_b200.so).  N=1 runs BASELINE config C2 (64x1024 image, 500k surfels).  N>1 is the
+keyframe-sharded window (weak scaling): every rank renders its own keyframe of the same
+surfel set and the per-surfel [P,10] gradient buffers are all-reduced with NCCL.
+
+Rank 0 prints ONE JSON line.  See DESIGN.md "Measurement" for every field.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "splat-loam_b200"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import scenes  # noqa: E402
+
+METRIC = "surfel raster fwd+bwd frames/s"
+UNIT = "frames/s"
+
+
+# ------------------------------------------------------------------ helpers ------------
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(p))["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "20"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+                for nm, v in zip(names, r[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def scene_tensors(cfg, keyframe, device, pinned=False):
+    s = scenes.make_scene(cfg, keyframe=keyframe)
+    t = {}
+    for k in ("means3D", "opacities", "scales", "rotations", "viewmatrix", "projmatrix", "dL_dout"):
+        x = torch.from_numpy(s[k])
+        t[k] = x.pin_memory() if pinned else x.to(device)
+    t["H"], t["W"] = s["H"], s["W"]
+    return t
+
+
+def algorithmic_bytes(P, N, Nc, HW):
+    """compulsory bytes per stage of one fwd+bwd frame."""
+    b = {
+        "preprocess": 132 * P,                 # 40 R + 84 W + scan 4 R + 4 W
+        "emit": 20 * P + 12 * N,               # duplicateWithKeys
+        "sort": (8 + 24 * 6 + 8) * N,          # histogram + 6 passes x (12 R + 12 W) + ranges
+        "render_forward": 76 * Nc + 48 * HW,
+        "render_backward": 180 * Nc + 48 * HW,  # 76 gather + 104 gradient RMW
+        "backward_preprocess": 236 * P,        # 112 zero-init + 88 R + 36 W
+    }
+    b["frame"] = sum(b.values())
+    return b
+
+
+def consumed_instances(nc, ranges, H, W):
+    """N_c = sum over tiles of max over the tile's pixels of n_contrib."""
+    gx, gy = (W + 15) // 16, (H + 15) // 16
+    last = nc[: H * W].reshape(H, W).astype(np.int64)
+    pad = np.zeros((gy * 16, gx * 16), dtype=np.int64)
+    pad[:H, :W] = last
+    return int(pad.reshape(gy, 16, gx, 16).max(axis=(1, 3)).sum())
+
+
+# ------------------------------------------------------------------ our arm ------------
+def run_ours(args, rank, world, local_rank):
+    import torch.distributed as dist
+    from diff_surfel_spherical_rasterization import _C
+    import splat_b200_native as native
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    t = scene_tensors(args.config, rank, dev)          # rank r renders keyframe r
+    H, W, P = t["H"], t["W"], t["means3D"].shape[0]
+    empty = torch.empty(0, device=dev)
+    gbuf = torch.empty((P, 10), dtype=torch.float32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB of L2
+
+    def frame(x):
+        R, allmap, radii, geom, binning, img = _C.rasterize_gaussians(
+            x["means3D"], x["opacities"], x["scales"], x["rotations"], 1.0, empty,
+            x["viewmatrix"], x["projmatrix"], H, W, False, False)
+        g = _C.rasterize_gaussians_backward(
+            x["means3D"], radii, x["scales"], x["rotations"], 1.0, empty, x["viewmatrix"],
+            x["projmatrix"], x["dL_dout"], geom, R, binning, img, False)
+        if world > 1:   # keyframe-sharded window: one all-reduce of the [P,10] buffer
+            torch.cat([g[2], g[1], g[4], g[5]], dim=1, out=gbuf)
+            dist.all_reduce(gbuf)
+        return R, allmap, g, (geom, binning, img)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        flush.zero_()
+        R, allmap, g, bufs = frame(t)
+    torch.cuda.synchronize()
+    nc = _C.debug_state(*bufs, "n_contrib").numpy().view(np.uint32)
+    rg = _C.debug_state(*bufs, "ranges").numpy()
+    Nc = consumed_instances(nc, rg, H, W)
+
+    # ---- device-resident throughput (`value`) + per-stage times ----
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    native.profile_enable(True)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+          for _ in range(args.steps)]
+    stages = {}
+    barrier()
+    for a, b in ev:
+        flush.zero_()                     # L2 flush between timed iterations (not timed)
+        a.record()
+        frame(t)
+        b.record()
+        b.synchronize()
+        for k, v in native.profile_read().items():
+            stages[k] = stages.get(k, 0.0) + v
+    barrier()
+    native.profile_enable(False)
+    total_ms = sum(a.elapsed_time(b) for a, b in ev)
+    clocks = sampler.stop() if sampler else None
+
+    # ---- end to end through the same calls with HOST buffers ----
+    hp = scene_tensors(args.config, rank, dev, pinned=True)
+    d_in = {k: torch.empty_like(v, device=dev) for k, v in hp.items() if torch.is_tensor(v)}
+    d_in["viewmatrix"].copy_(hp["viewmatrix"]); d_in["projmatrix"].copy_(hp["projmatrix"])
+    h_map = torch.empty((7, H, W), dtype=torch.float32).pin_memory()
+    h_grad = torch.empty((P, 10), dtype=torch.float32).pin_memory()
+    keys = ("means3D", "opacities", "scales", "rotations", "dL_dout")
+    h2d = sum(hp[k].numel() * 4 for k in keys)
+    d2h = h_map.numel() * 4 + h_grad.numel() * 4
+
+    def e2e_step():
+        for k in keys:
+            d_in[k].copy_(hp[k], non_blocking=True)
+        R, allmap, g, _ = frame(d_in)
+        if world == 1:
+            torch.cat([g[2], g[1], g[4], g[5]], dim=1, out=gbuf)
+        h_map.copy_(allmap, non_blocking=True)
+        h_grad.copy_(gbuf, non_blocking=True)
+
+    for _ in range(3):
+        e2e_step()
+    ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+           for _ in range(args.steps)]
+    barrier()
+    for a, b in ev2:
+        flush.zero_()
+        a.record()
+        e2e_step()
+        b.record()
+        b.synchronize()
+    barrier()
+    e2e_ms = sum(a.elapsed_time(b) for a, b in ev2)
+
+    if world > 1:   # max over ranks, on the device timeline
+        tt = torch.tensor([total_ms, e2e_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        total_ms, e2e_ms = float(tt[0]), float(tt[1])
+    if rank != 0:
+        return None
+
+    ms_per_step = total_ms / args.steps
+    value = world * 1e3 / ms_per_step
+    ab = algorithmic_bytes(P, R, Nc, H * W)
+    peak, peak_src = measured_peak_gbs()
+    stage_ms = {k: v / args.steps for k, v in stages.items()}
+    dom = max(stage_ms, key=stage_ms.get) if stage_ms else "render_backward"
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dom)
+    except Exception:
+        pass
+    achieved = ab[dom] / (stage_ms[dom] * 1e-3) / 1e9 if stage_ms.get(dom) else None
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.config}: {H}x{W} spherical range image, {P} surfels, "
+                               f"fwd+bwd per frame, one keyframe per GPU"
+                               + (", NCCL all-reduce of the [P,10] gradients" if world > 1 else ""),
+                   "instances": R, "consumed_instances": Nc,
+                   "l2": "256 MB buffer written between timed steps",
+                   "parallelism": f"keyframe-sharded x{world}"},
+        "e2e": {"value": world * 1e3 / (e2e_ms / args.steps), "unit": UNIT,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": 11 * args.steps,
+        "stage_ms": stage_ms,
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak,
+                     "peak_source": peak_src, "unit": "GB/s",
+                     "frac": achieved / peak if achieved else None, "traffic": traffic,
+                     "algorithmic_bytes": ab[dom]},
+        "frame_roofline": {"algorithmic_bytes": ab["frame"],
+                           "achieved": ab["frame"] / (ms_per_step * 1e-3) / 1e9, "unit": "GB/s",
+                           "frac": ab["frame"] / (ms_per_step * 1e-3) / 1e9 / peak},
+        "clocks": clocks,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(args.config)
+    return line
+
+
+# ------------------------------------------------------------------ baselines ----------
+def cpu_baseline(cfg, full=True):
+    """The plain-C oracle (a PORT of the reference algorithm; the reference itself has no CPU
+    implementation) timed on the host cores for one whole fwd+bwd frame of the workload."""
+    from oracle import oracle
+    s = scenes.make_scene(cfg)
+    oracle.build()
+    t0 = time.perf_counter()
+    f = oracle.rasterize_forward(s["means3D"], s["scales"], s["rotations"], s["opacities"],
+                                 s["viewmatrix"], s["projmatrix"], s["H"], s["W"])
+    oracle.rasterize_backward(f, s["dL_dout"])
+    dt = time.perf_counter() - t0
+    return {"value": 1.0 / dt, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+            "sample": f"1 full fwd+bwd frame of {cfg} ({dt:.2f} s, OpenMP on all cores; "
+                      "preprocess/sort single-threaded)"}
+
+
+def run_reference(args, rank, world, local_rank):
+    """The UNMODIFIED reference CUDA rasterizer (oracle/_ref, built from /root/reference by
+    oracle/Makefile) on the same frames.  The reference has no CPU implementation of this path;
+    its CUDA build is what BASELINE.json's target (>= 3x) is quoted against, so that is what
+    this arm times, with the CPU oracle port reported beside it."""
+    if rank != 0:
+        return None
+    import reflib
+    line = {"impl": "reference", "metric": METRIC, "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic"}
+    if not reflib.available():
+        cb = cpu_baseline(args.config)
+        line.update(value=cb["value"], ms_per_step=1e3 / cb["value"], cpu_baseline=cb,
+                    config={"workload": f"{args.config} on the CPU oracle port (reference CUDA "
+                                        "build oracle/_ref or GPU not available)"},
+                    e2e={"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0,
+                         "d2h_bytes_per_step": 0})
+        return line
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    t = scene_tensors(args.config, 0, dev)
+    H, W, P = t["H"], t["W"], t["means3D"].shape[0]
+    opa = t["opacities"].reshape(-1).contiguous()
+    ref = reflib.RefRasterizer()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def frame(x, o):
+        R, out, radii = ref.forward(x["means3D"], o, x["scales"], x["rotations"],
+                                    x["viewmatrix"], x["projmatrix"], H, W, sync=False)
+        g = ref.backward(x["dL_dout"], sync=False)
+        return R, out, g
+
+    for _ in range(max(args.warmup, 3)):
+        frame(t, opa)
+    torch.cuda.synchronize()
+
+    def timed(fn):
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+              for _ in range(args.steps)]
+        torch.cuda.synchronize()
+        for a, b in ev:
+            flush.zero_()
+            a.record()
+            fn()
+            b.record()
+            b.synchronize()
+        torch.cuda.synchronize()
+        return sum(a.elapsed_time(b) for a, b in ev) / args.steps
+
+    ms = timed(lambda: frame(t, opa))
+    hp = scene_tensors(args.config, 0, dev, pinned=True)
+    d_in = {k: torch.empty_like(v, device=dev) for k, v in hp.items() if torch.is_tensor(v)}
+    d_in["viewmatrix"].copy_(hp["viewmatrix"]); d_in["projmatrix"].copy_(hp["projmatrix"])
+    h_map = torch.empty((7, H, W), dtype=torch.float32).pin_memory()
+    h_grad = torch.empty((P, 10), dtype=torch.float32).pin_memory()
+    gbuf = torch.empty((P, 10), dtype=torch.float32, device=dev)
+    keys = ("means3D", "opacities", "scales", "rotations", "dL_dout")
+
+    def e2e_step():
+        for k in keys:
+            d_in[k].copy_(hp[k], non_blocking=True)
+        R, out, g = frame(d_in, d_in["opacities"].reshape(-1))
+        torch.cat([g["means3D"], g["opacity"], g["scales"], g["rotations"]], dim=1, out=gbuf)
+        h_map.copy_(out, non_blocking=True)
+        h_grad.copy_(gbuf, non_blocking=True)
+
+    for _ in range(3):
+        e2e_step()
+    ms_e2e = timed(e2e_step)
+    line.update(
+        value=1e3 / ms, ms_per_step=ms,
+        config={"workload": f"{args.config}: {H}x{W}, {P} surfels, fwd+bwd per frame, UNMODIFIED "
+                            "reference CUDA rasterizer (oracle/_ref), 1 GPU",
+                "l2": "256 MB buffer written between timed steps"},
+        kind="reference",
+        e2e={"value": 1e3 / ms_e2e, "unit": UNIT,
+             "h2d_bytes_per_step": sum(hp[k].numel() * 4 for k in keys),
+             "d2h_bytes_per_step": h_map.numel() * 4 + h_grad.numel() * 4})
+    if not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(args.config)
+    return line
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="C2", choices=list(scenes.CONFIGS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        line = run_reference(args, rank, world, local_rank)
+        if line is not None:
+            print(json.dumps(line), flush=True)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world,
+                                device_id=torch.device("cuda", local_rank))
+    line = run_ours(args, rank, world, local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+    if line is not None:
+        print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

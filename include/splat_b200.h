@@ -135,6 +135,17 @@ SPLAT_API size_t sknn_workspace_bytes(int P);
 SPLAT_API int sknn_dist2(int P, const float *points, float *mean_dists, void *workspace,
                size_t workspace_bytes, void *stream);
 
+/* ---- per-stage device timing ----------------------------------------------------
+ * No counterpart in the reference (its only timing is wall-clock prints in
+ * DSSR/tests/test_backward.py:54-85).  While enabled (per host thread), dssr_forward /
+ * dssr_backward bracket each stage with CUDA events on the launch stream.  After the
+ * caller has synchronised that stream, splat_profile_read returns the stages seen since
+ * the last read: their static names and elapsed milliseconds; the return value is the
+ * stage count.  Stages: preprocess, emit, sort, render_forward, render_backward,
+ * backward_preprocess. */
+SPLAT_API int splat_profile_enable(int on);
+SPLAT_API int splat_profile_read(int max_stages, const char **names, float *ms);
+
 SPLAT_API const char *splat_last_error(void);
 SPLAT_API int splat_abi_version(void);
 

@@ -52,6 +52,38 @@ struct Trace {
   }
 };
 
+// Optional per-stage device timing (splat_profile_*): CUDA events recorded on the launch
+// stream around each stage, read back by the caller after it has synchronised.
+struct Prof {
+  static constexpr int MAXS = 16;
+  bool on = false;
+  int n = 0;
+  cudaEvent_t beg[MAXS], end[MAXS];
+  const char *name[MAXS];
+  bool made = false;
+  int slot(const char *nm) {
+    for (int i = 0; i < n; i++)
+      if (name[i] == nm) return i;
+    if (n == MAXS) return -1;
+    name[n] = nm;
+    return n++;
+  }
+};
+thread_local Prof g_prof;
+
+struct ProfScope {
+  int s = -1;
+  cudaStream_t st;
+  ProfScope(const char *nm, cudaStream_t st_) : st(st_) {
+    if (!g_prof.on) return;
+    s = g_prof.slot(nm);
+    if (s >= 0) cudaEventRecord(g_prof.beg[s], st);
+  }
+  ~ProfScope() {
+    if (s >= 0) cudaEventRecord(g_prof.end[s], st);
+  }
+};
+
 int ensure_host_scratch() {
   if (!g_pinned) CUDA_TRY(cudaHostAlloc((void **)&g_pinned, 64, cudaHostAllocPortable));
   if (!g_event) CUDA_TRY(cudaEventCreateWithFlags(&g_event, cudaEventDisableTiming));
@@ -68,11 +100,20 @@ int run_binning_and_render(const dssr_forward_args *a, const FwdParams &fp,
   if (!bptr) return fail("binning_alloc(%zu) returned NULL", bl.total);
   BinView bv = make_bin_view(bptr, capacity, keep, sp);
   CUDA_TRY(cudaMemsetAsync(bv.hist, 0, bv.zero_bytes, st));
-  launch_emit(fp, gv, iv, bv, sp, capacity, st);
+  {
+    ProfScope ps("emit", st);
+    launch_emit(fp, gv, iv, bv, sp, capacity, st);
+  }
   LAUNCH_CHECK(dbg, st, "emit");
-  launch_sort(gv, iv, bv, sp, capacity, st);
+  {
+    ProfScope ps("sort", st);
+    launch_sort(gv, iv, bv, sp, capacity, st);
+  }
   LAUNCH_CHECK(dbg, st, "sort");
-  launch_render_forward(fp, gv, iv, bv, capacity, st);
+  {
+    ProfScope ps("render_forward", st);
+    launch_render_forward(fp, gv, iv, bv, capacity, st);
+  }
   LAUNCH_CHECK(dbg, st, "render_forward");
   return 0;
 }
@@ -100,6 +141,32 @@ size_t dssr_binning_bytes(int64_t capacity, int W, int H, int P, int keep_unsort
   ImageLayout il(W, H);
   SortPlan sp(P, il.tiles);
   return BinLayout((size_t)(capacity < 0 ? 0 : capacity), keep_unsorted, sp).total;
+}
+
+int splat_profile_enable(int on) {
+  if (on && !g_prof.made) {
+    for (int i = 0; i < Prof::MAXS; i++) {
+      if (cudaEventCreate(&g_prof.beg[i]) != cudaSuccess ||
+          cudaEventCreate(&g_prof.end[i]) != cudaSuccess)
+        return fail("splat_profile_enable: cudaEventCreate failed");
+    }
+    g_prof.made = true;
+  }
+  g_prof.on = on != 0;
+  g_prof.n = 0;
+  return 0;
+}
+
+int splat_profile_read(int max_stages, const char **names, float *ms) {
+  int n = g_prof.n < max_stages ? g_prof.n : max_stages;
+  for (int i = 0; i < n; i++) {
+    float t = 0.f;
+    if (cudaEventElapsedTime(&t, g_prof.beg[i], g_prof.end[i]) != cudaSuccess) t = -1.f;
+    if (names) names[i] = g_prof.name[i];
+    if (ms) ms[i] = t;
+  }
+  g_prof.n = 0;
+  return n;
 }
 
 int dssr_forward(const dssr_forward_args *a, int *num_rendered) {
@@ -150,10 +217,12 @@ int dssr_forward(const dssr_forward_args *a, int *num_rendered) {
   fp.viewmatrix = a->viewmatrix; fp.projmatrix = a->projmatrix;
   fp.out_maps = a->out_maps; fp.radii = a->radii;
 
-  launch_preprocess(fp, gv, iv, st);
+  {
+    ProfScope ps("preprocess", st);
+    launch_preprocess(fp, gv, iv, st);
+    launch_chunk_scan(gv, st);
+  }
   LAUNCH_CHECK(dbg, st, "preprocess");
-  launch_chunk_scan(gv, st);
-  LAUNCH_CHECK(dbg, st, "chunk_scan");
   CUDA_TRY(cudaMemcpyAsync(g_pinned, &gv.hdr->num_rendered, 8, cudaMemcpyDeviceToHost, st));
   CUDA_TRY(cudaEventRecord(g_event, st));
   tr.lap("enqueue preprocess");
@@ -214,9 +283,15 @@ int dssr_backward(const dssr_backward_args *a) {
   bp.dL_dopacity = a->dL_dopacity; bp.dL_dmeans3D = a->dL_dmeans3D;
   bp.dL_dtransMat = a->dL_dtransMat; bp.dL_dscales = a->dL_dscales;
   bp.dL_drotations = a->dL_drotations;
-  launch_render_backward(bp, gv, iv, bv, st);
+  {
+    ProfScope ps("render_backward", st);
+    launch_render_backward(bp, gv, iv, bv, st);
+  }
   LAUNCH_CHECK(dbg, st, "render_backward");
-  launch_backward_preprocess(bp, st);
+  {
+    ProfScope ps("backward_preprocess", st);
+    launch_backward_preprocess(bp, st);
+  }
   LAUNCH_CHECK(dbg, st, "backward_preprocess");
   return 0;
 }

@@ -52,7 +52,8 @@ class DssrBackwardArgs(ctypes.Structure):
 EXPORTS = (
     "dssr_forward", "dssr_backward", "dssr_mark_visible", "dssr_geometry_bytes",
     "dssr_image_bytes", "dssr_binning_bytes", "dssr_debug_state", "sknn_workspace_bytes",
-    "sknn_dist2", "splat_last_error", "splat_abi_version",
+    "sknn_dist2", "splat_last_error", "splat_abi_version", "splat_profile_enable",
+    "splat_profile_read",
 )
 
 _lib = None
@@ -96,8 +97,25 @@ def load():
     lib.splat_last_error.restype = ctypes.c_char_p
     lib.splat_abi_version.argtypes = []
     lib.splat_abi_version.restype = ctypes.c_int
+    lib.splat_profile_enable.argtypes = [ctypes.c_int]
+    lib.splat_profile_enable.restype = ctypes.c_int
+    lib.splat_profile_read.argtypes = [ctypes.c_int, ctypes.POINTER(ctypes.c_char_p),
+                                       ctypes.POINTER(ctypes.c_float)]
+    lib.splat_profile_read.restype = ctypes.c_int
     _lib = lib
     return lib
+
+
+def profile_enable(on=True):
+    check(load().splat_profile_enable(int(bool(on))))
+
+
+def profile_read():
+    """{stage: milliseconds} for the stages run since the last read (synchronise first)."""
+    names = (ctypes.c_char_p * 16)()
+    ms = (ctypes.c_float * 16)()
+    n = load().splat_profile_read(16, names, ms)
+    return {names[i].decode(): float(ms[i]) for i in range(n)}
 
 
 def last_error():
