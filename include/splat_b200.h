@@ -135,6 +135,23 @@ SPLAT_API size_t sknn_workspace_bytes(int P);
 SPLAT_API int sknn_dist2(int P, const float *points, float *mean_dists, void *workspace,
                size_t workspace_bytes, void *stream);
 
+/* distCUDA2 for callers that cannot allocate device memory (no counterpart in the
+ * reference, which cudaMallocs inside every call: SKNN/simple_knn.cu:188-221).  Meant for
+ * hosts without an allocator of their own: a latency-bound sensor or tracking thread
+ * (cudaMalloc / cudaFree serialise the device), a process whose GPU memory already belongs
+ * to another framework's caching allocator, a plug-in that may not make allocating CUDA
+ * calls.  Inputs and output as sknn_dist2; the scratch is a file-scope device array inside
+ * the library (about 3 MB on every GPU that loads it, held until exit), so:
+ *   - P must not exceed SKNN_STATIC_MAX_POINTS, larger clouds are refused with an error;
+ *   - the first call on a device resolves the array's address on that device; make it
+ *     before any stream capture begins;
+ *   - all calls share the array (it keeps the previous call's contents; what has to start
+ *     at zero is cleared at the start of each call): calls whose GPU work overlaps race,
+ *     serialise them;
+ *   - no cudaMalloc, cudaFree or allocating library routine is called. */
+#define SKNN_STATIC_MAX_POINTS 65536
+SPLAT_API int sknn_dist2_static(int P, const float *points, float *mean_dists, void *stream);
+
 /* ---- per-stage device timing ----------------------------------------------------
  * No counterpart in the reference (its only timing is wall-clock prints in
  * DSSR/tests/test_backward.py:54-85).  While enabled (per host thread), dssr_forward /

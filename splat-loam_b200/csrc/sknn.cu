@@ -305,3 +305,71 @@ int sknn_dist2(int P, const float *points, float *mean_dists, void *workspace,
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------
+// sknn_dist2_static — distCUDA2 for callers that must not allocate device memory.
+//
+// Who needs this: code that sits on top of this C-ABI but owns no allocator of its own.
+// Typical cases are a sensor / tracking thread with a latency budget (cudaMalloc and
+// cudaFree serialise the whole device and can stall a frame), a process in which another
+// framework's caching allocator has already claimed the GPU's memory (a second allocator
+// asking the driver for more can simply fail), or a plug-in whose host forbids allocating
+// CUDA calls in its callbacks.  Such a caller passes only the points and the output array;
+// the scratch that sknn_dist2 takes from its caller lives instead in the file-scope device
+// array below, which every GPU that loads this library carries until the process exits.
+//
+// Limits and rules (also in include/splat_b200.h):
+//   * at most SKNN_STATIC_MAX_POINTS points per call; larger clouds are refused with an
+//     error, nothing is launched;
+//   * the first call on a device looks up that device's address of the array
+//     (cudaGetSymbolAddress with the device current) and caches it; make that first call
+//     outside of any stream capture;
+//   * all calls share the one array and it keeps whatever the previous call left there.
+//     The tables that must start at zero (digit histograms, tickets, look-back status) are
+//     cleared at the start of every call by sknn_dist2 itself (a cudaMemsetAsync on the
+//     caller's stream, not an allocation); everything else is overwritten before it is read;
+//   * because the array is shared, two calls whose GPU work overlaps (different streams, or
+//     different host threads) race on it: serialise them;
+//   * no cudaMalloc, cudaFree or allocating library routine is called on any path.
+#include <mutex>
+
+#define SKNN_STATIC_BYTES (3u << 20)   // >= KnnLayout(SKNN_STATIC_MAX_POINTS).total (2.4 MB)
+
+static __device__ __align__(256) unsigned char g_sknn_static_scratch[SKNN_STATIC_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void *g_static_scratch_ptr[kMaxDevices];   // device ordinal -> device address of the array
+std::mutex g_static_scratch_mu;
+}  // namespace
+
+extern "C" int sknn_dist2_static(int P, const float *points, float *mean_dists, void *stream) {
+  if (P < 0) return splat_fail("sknn_dist2_static: P < 0");
+  if (P > SKNN_STATIC_MAX_POINTS)
+    return splat_fail("sknn_dist2_static: %d points exceed the static scratch limit of %d; use "
+                      "sknn_dist2 with a caller-owned workspace", P, SKNN_STATIC_MAX_POINTS);
+  if (P == 0) return 0;
+  if (KnnLayout(P).total > SKNN_STATIC_BYTES)
+    return splat_fail("sknn_dist2_static: internal error, scratch layout larger than the array");
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices)
+    return splat_fail("sknn_dist2_static: cudaGetDevice failed or device ordinal %d unsupported: %s",
+                      dev, cudaGetErrorString(e));
+  void *scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+    if (!g_static_scratch_ptr[dev]) {
+      // In host code the array's name is only a handle; the address a kernel can use on
+      // THIS device has to be asked for, with this device current.
+      void *p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_sknn_static_scratch);
+      if (e != cudaSuccess || !p)
+        return splat_fail("sknn_dist2_static: cudaGetSymbolAddress failed: %s",
+                          cudaGetErrorString(e));
+      g_static_scratch_ptr[dev] = p;
+    }
+    scratch = g_static_scratch_ptr[dev];
+  }
+  return sknn_dist2(P, points, mean_dists, scratch, SKNN_STATIC_BYTES, stream);
+}

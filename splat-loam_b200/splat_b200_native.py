@@ -53,7 +53,7 @@ EXPORTS = (
     "dssr_forward", "dssr_backward", "dssr_mark_visible", "dssr_geometry_bytes",
     "dssr_image_bytes", "dssr_binning_bytes", "dssr_debug_state", "sknn_workspace_bytes",
     "sknn_dist2", "splat_last_error", "splat_abi_version", "splat_profile_enable",
-    "splat_profile_read",
+    "splat_profile_read", "sknn_dist2_static",
 )
 
 _lib = None
@@ -93,6 +93,8 @@ def load():
     lib.sknn_dist2.argtypes = [ctypes.c_int, c_float_p, c_float_p, ctypes.c_void_p,
                                ctypes.c_size_t, ctypes.c_void_p]
     lib.sknn_dist2.restype = ctypes.c_int
+    lib.sknn_dist2_static.argtypes = [ctypes.c_int, c_float_p, c_float_p, ctypes.c_void_p]
+    lib.sknn_dist2_static.restype = ctypes.c_int
     lib.splat_last_error.argtypes = []
     lib.splat_last_error.restype = ctypes.c_char_p
     lib.splat_abi_version.argtypes = []
