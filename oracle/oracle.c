@@ -459,3 +459,80 @@ void orc_knn_range(int P, const float *pts, int q0, int q1, float *out) {
     out[i] = (b0 + b1 + b2) / 3.0f;
   }
 }
+
+/* Developer statistics (not a reference restatement): for every 8x4 pixel sub-tile, over the
+ * list prefix its pixels traverse, count entries / entries with at least one pixel passing
+ * the alpha test / passing (pixel, entry) pairs.  stats[0..3] = traversed, true_hit, pairs,
+ * entries whose box (xmin,xmax,ymin,ymax per surfel, may be NULL) overlaps the sub-tile. */
+void orc_pair_stats(int W, int H, const uint32_t *ranges, const uint32_t *point_list,
+                    const float *xy, const float *T, const float *nrm_opa, const float *proj,
+                    const uint32_t *n_contrib, const float *boxes, double *stats) {
+  const int gx = (W + TILE - 1) / TILE;
+  double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+#pragma omp parallel for schedule(dynamic, 4) reduction(+ : s0, s1, s2, s3)
+  for (int st = 0; st < ((W + 7) / 8) * ((H + 3) / 4); st++) {
+    int sx = (st % ((W + 7) / 8)) * 8, sy = (st / ((W + 7) / 8)) * 4;
+    int tile = (sy / TILE) * gx + sx / TILE;
+    uint32_t r0 = ranges[2 * tile];
+    uint32_t trav = 0;
+    ray_t rays[32];
+    for (int l = 0; l < 32; l++) {
+      int px = sx + (l & 7), py = sy + (l >> 3);
+      rays[l] = make_ray((float)px, (float)py, proj);
+      if (px < W && py < H && n_contrib[(size_t)py * W + px] > trav) trav = n_contrib[(size_t)py * W + px];
+    }
+    for (uint32_t e = 0; e < trav; e++) {
+      uint32_t id = point_list[r0 + e];
+      int any = 0;
+      for (int l = 0; l < 32; l++) {
+        int px = sx + (l & 7), py = sy + (l >> 3);
+        if (px >= W || py >= H) continue;
+        hit_t h;
+        if (intersect(&rays[l], (float)px, (float)py, T + 12 * (size_t)id, xy + 2 * (size_t)id,
+                      nrm_opa[4 * (size_t)id + 3], &h)) { any = 1; s2 += 1; }
+      }
+      s0 += 1; s1 += any;
+      if (boxes) {
+        const float *b = boxes + 4 * (size_t)id;
+        if (!(b[2] > sy + 3) && !(b[3] < sy) && !(b[0] > sx + 7) && !(b[1] < sx)) s3 += 1;
+      }
+    }
+  }
+  stats[0] = s0; stats[1] = s1; stats[2] = s2; stats[3] = s3;
+}
+
+/* Developer statistics per 4x4 sub-tile: out[st*3+0..2] = traversed entries, entries whose
+ * box overlaps the sub-tile, entries with at least one passing pixel. */
+void orc_subtile_stats(int W, int H, const uint32_t *ranges, const uint32_t *point_list,
+                       const float *xy, const float *T, const float *nrm_opa, const float *proj,
+                       const uint32_t *n_contrib, const float *boxes, uint32_t *out) {
+  const int gx = (W + TILE - 1) / TILE;
+  const int nsx = (W + 3) / 4, nsy = (H + 3) / 4;
+#pragma omp parallel for schedule(dynamic, 4)
+  for (int st = 0; st < nsx * nsy; st++) {
+    int sx = (st % nsx) * 4, sy = (st / nsx) * 4;
+    int tile = (sy / TILE) * gx + sx / TILE;
+    uint32_t r0 = ranges[2 * tile], trav = 0, nb = 0, nt = 0;
+    ray_t rays[16];
+    for (int l = 0; l < 16; l++) {
+      int px = sx + (l & 3), py = sy + (l >> 2);
+      rays[l] = make_ray((float)px, (float)py, proj);
+      if (px < W && py < H && n_contrib[(size_t)py * W + px] > trav) trav = n_contrib[(size_t)py * W + px];
+    }
+    for (uint32_t e = 0; e < trav; e++) {
+      uint32_t id = point_list[r0 + e];
+      const float *b = boxes + 4 * (size_t)id;
+      if (b[2] > sy + 3 || b[3] < sy || b[0] > sx + 3 || b[1] < sx) continue;
+      nb++;
+      int any = 0;
+      for (int l = 0; l < 16 && !any; l++) {
+        int px = sx + (l & 3), py = sy + (l >> 2);
+        hit_t h;
+        if (px < W && py < H && intersect(&rays[l], (float)px, (float)py, T + 12 * (size_t)id,
+                                          xy + 2 * (size_t)id, nrm_opa[4 * (size_t)id + 3], &h)) any = 1;
+      }
+      nt += any;
+    }
+    out[3 * st] = trav; out[3 * st + 1] = nb; out[3 * st + 2] = nt;
+  }
+}

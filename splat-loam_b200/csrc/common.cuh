@@ -65,7 +65,7 @@ struct GeomLayout {
 };
 
 struct ImageLayout {
-  size_t final_T, n_contrib, ranges, total;
+  size_t final_T, n_contrib, ranges, tile_order, total;
   int tiles_x, tiles_y, tiles;
   __host__ ImageLayout(int W, int H) {
     tiles_x = (W + SPLAT_TILE - 1) / SPLAT_TILE;
@@ -76,6 +76,7 @@ struct ImageLayout {
     final_T = o;   o = align_up(o + HW * 12, 256);
     n_contrib = o; o = align_up(o + HW * 8, 256);
     ranges = o;    o = align_up(o + (size_t)tiles * 8, 256);
+    tile_order = o; o = align_up(o + (size_t)tiles * 4, 256);
     total = o + 256;
   }
 };
@@ -114,11 +115,15 @@ struct BinHeader {
   uint32_t magic;
   uint32_t capacity;
   uint32_t keep_unsorted;
-  uint32_t pad[5];
+  uint32_t pad;
+  // byte offset (from the aligned buffer start) of sub_mask: the backward only knows
+  // num_rendered, not the capacity the forward laid the buffer out with
+  unsigned long long off_sub_mask;
+  uint32_t pad2[2];
 };
 
 struct BinLayout {
-  size_t words_a, words_b, keys, point_list, keys_unsorted, hist, digit_base, status,
+  size_t words_a, words_b, keys, point_list, sub_mask, keys_unsorted, hist, digit_base, status,
       tickets, total;
   size_t status_bytes, hist_bytes;
   size_t status_off[SORT_MAX_PASSES];  // element offset of each pass in `status`
@@ -133,6 +138,7 @@ struct BinLayout {
     keys = o;       o = align_up(o + C * 8, 256);
     words_a = o;    o = align_up(o + C * 8, 256);
     words_b = o;    o = align_up(o + C * 8, 256);
+    sub_mask = o;   o = align_up(o + C * 2, 256);
     keys_unsorted = o;
     if (keep_unsorted) o = align_up(o + C * 8, 256);
     // [hist | tickets | status] are zeroed with ONE memset per forward
@@ -174,12 +180,15 @@ struct ImageView {
   float *final_T;
   uint32_t *n_contrib;
   uint2 *ranges;
+  uint32_t *tile_order;   // tiles sorted by decreasing list length (work scheduling)
   int tiles_x, tiles_y, tiles;
 };
 struct BinView {
   BinHeader *hdr;
   unsigned long long *words_a, *words_b, *keys, *keys_unsorted;
   uint32_t *point_list;
+  uint16_t *sub_mask;     // per sorted instance: which 4x4 sub-tiles of its tile it can touch
+  size_t off_sub_mask;
   uint32_t *hist, *digit_base, *status, *tickets;
   size_t status_off[SORT_MAX_PASSES];
   size_t zero_bytes;  // [hist .. end of status) is one contiguous region to clear
@@ -209,6 +218,7 @@ static inline ImageView make_image_view(const char *buf, int W, int H) {
   v.final_T = (float *)(b + L.final_T);
   v.n_contrib = (uint32_t *)(b + L.n_contrib);
   v.ranges = (uint2 *)(b + L.ranges);
+  v.tile_order = (uint32_t *)(b + L.tile_order);
   v.tiles_x = L.tiles_x;
   v.tiles_y = L.tiles_y;
   v.tiles = L.tiles;
@@ -225,6 +235,8 @@ static inline BinView make_bin_view(const char *buf, size_t C, int keep_unsorted
   v.keys = (unsigned long long *)(b + L.keys);
   v.keys_unsorted = keep_unsorted ? (unsigned long long *)(b + L.keys_unsorted) : nullptr;
   v.point_list = (uint32_t *)(b + L.point_list);
+  v.sub_mask = (uint16_t *)(b + L.sub_mask);
+  v.off_sub_mask = L.sub_mask;
   v.hist = (uint32_t *)(b + L.hist);
   v.digit_base = (uint32_t *)(b + L.digit_base);
   v.status = (uint32_t *)(b + L.status);
@@ -255,12 +267,19 @@ void launch_chunk_scan(const GeomView &g, cudaStream_t s);
 void launch_emit(const FwdParams &p, const GeomView &g, const ImageView &im,
                  const BinView &b, const SortPlan &sp, uint32_t capacity,
                  cudaStream_t s);
-void launch_sort(const GeomView &g, const ImageView &im, const BinView &b,
+void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, const BinView &b,
                  const SortPlan &sp, uint32_t capacity, cudaStream_t s);
 void launch_digit_scan(const uint32_t *hist, uint32_t *digit_base, int npass, uint2 *ranges,
                        int tiles, int tile_pass_single, int nrepl, cudaStream_t s);
+struct MaskParams {          // what the last sort pass needs to emit sub_mask (may be all 0)
+  uint16_t *sub_mask;
+  const float4 *cull;
+  const float *projmatrix;
+  int tiles_x, H;
+};
 unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long *b,
                                        unsigned long long *keys_out, uint32_t *plist_out,
+                                       MaskParams mp,
                                        const uint32_t *num_ptr, uint32_t capacity,
                                        uint32_t *status, const size_t *status_off,
                                        uint32_t *tickets, const uint32_t *digit_base,

@@ -107,7 +107,7 @@ int run_binning_and_render(const dssr_forward_args *a, const FwdParams &fp,
   LAUNCH_CHECK(dbg, st, "emit");
   {
     ProfScope ps("sort", st);
-    launch_sort(gv, iv, bv, sp, capacity, st);
+    launch_sort(fp, gv, iv, bv, sp, capacity, st);
   }
   LAUNCH_CHECK(dbg, st, "sort");
   {

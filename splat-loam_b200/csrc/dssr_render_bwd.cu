@@ -6,143 +6,217 @@
 //   quat_to_rotmat_vjp          auxiliary.h:300-339
 //
 // The reference issues 13 global float atomicAdds per (pixel, surfel) pair, all 256
-// threads of a tile hitting the same 13 addresses.  Here a warp owns an 8x4 pixel
+// threads of a tile hitting the same 13 addresses.  Here a warp owns a 4x4 pixel
 // sub-tile, walks its tile's list back to front from the furthest entry any of its
 // pixels blended, skips entries whose cull box misses the sub-tile (exact, see
-// dssr_render_fwd.cu), and for every surviving entry reduces the 13 per-pixel
-// contributions across the warp with a 16-shuffle transposed butterfly, after which 13
-// lanes issue ONE atomic instruction (one RED per component per warp instead of up to
-// 32).  The reference's backward is not the adjoint of its forward (SURVEY.md §8 a10,
+// dssr_render_fwd.cu), evaluates the survivors two at a time (one per half warp) and
+// reduces each surfel's 13 per-pixel contributions inside its half warp with a
+// 15-shuffle transposed butterfly, after which 13 lanes issue ONE atomic instruction
+// (one RED per component per sub-tile instead of one per pixel).  The reference's backward is not the adjoint of its forward (SURVEY.md §8 a10,
 // quirks Q1-Q4, Q7); it is reproduced as written.
 #include "raster_math.cuh"
 
 namespace {
 
-constexpr int BW_WARPS = 4;
-constexpr int SUB_W = 8, SUB_H = 4;
+constexpr int SUB = 4;                                            // 4x4 pixels per warp
+constexpr int SUBS_PER_TILE = (SPLAT_TILE / SUB) * (SPLAT_TILE / SUB);   // 16
 
-__global__ void __launch_bounds__(BW_WARPS * 32)
-render_backward_kernel(const uint2 *__restrict__ ranges,
+// Per-pixel state of the reverse traversal (backward.cu:62-98) and its constants.
+struct BackState {
+  float T, last_dL_dT, accum_depth_rec, accum_alpha_rec, accum_n0, accum_n1, accum_n2;
+  float last_alpha, last_depth, last_n0, last_n1, last_n2;
+};
+struct PixelConst {
+  float gD, gA, gN0, gN1, gN2, gMed, gReg, final_D, final_D2, final_A;
+  uint32_t last_contributor, median_contributor;
+};
+struct StepOut {
+  float T, w, dL_dalpha, dLd_depth;
+};
+
+// backward.cu:183-237 for one surviving (pixel, surfel) pair, as written (quirks kept)
+__device__ __forceinline__ StepOut recur(BackState &b, const PixelConst &c, float alpha,
+                                         float depth, float nx, float ny, float nz, uint32_t pos) {
+  StepOut o;
+  b.T = __fdiv_rn(b.T, 1.0f - alpha);
+  o.T = b.T;
+  o.w = alpha * b.T;
+  const float dL_dweight = (c.final_D2 + depth * depth * c.final_A - 2.0f * depth * c.final_D) * c.gReg;
+  float dL_dalpha = dL_dweight - b.last_dL_dT;
+  b.last_dL_dT = dL_dweight * alpha + (1.0f - alpha) * b.last_dL_dT;
+  float dLd_depth = 2.0f * (b.T * alpha) * (depth * c.final_A - c.final_D) * c.gReg;
+  if (pos == c.median_contributor - 1u) dLd_depth += c.gMed;
+  dLd_depth += o.w * c.gD;
+  b.accum_depth_rec = b.last_alpha * b.last_depth + (1.0f - b.last_alpha) * b.accum_depth_rec;
+  b.last_depth = depth;
+  dL_dalpha += (depth - b.accum_depth_rec) * c.gD;
+  b.accum_n0 = b.last_alpha * b.last_n0 + (1.0f - b.last_alpha) * b.accum_n0;
+  b.accum_n1 = b.last_alpha * b.last_n1 + (1.0f - b.last_alpha) * b.accum_n1;
+  b.accum_n2 = b.last_alpha * b.last_n2 + (1.0f - b.last_alpha) * b.accum_n2;
+  b.last_n0 = nx; b.last_n1 = ny; b.last_n2 = nz;
+  dL_dalpha += (nx - b.accum_n0) * c.gN0;
+  dL_dalpha += (ny - b.accum_n1) * c.gN1;
+  dL_dalpha += (nz - b.accum_n2) * c.gN2;
+  b.accum_alpha_rec = b.last_alpha + (1.0f - b.last_alpha) * b.accum_alpha_rec;
+  dL_dalpha += (1.0f - b.accum_alpha_rec) * c.gA;
+  dL_dalpha *= b.T;
+  b.last_alpha = alpha;
+  o.dL_dalpha = dL_dalpha;
+  o.dLd_depth = dLd_depth;
+  return o;
+}
+
+// One WARP per CTA = one 4x4 sub-tile, CTAs in order of decreasing tile list length.  Same
+// traversal machinery as the forward (sub-tile masks, double-buffered staging), walked back
+// to front; lanes 0-15 handle the later surfel of a pair, lanes 16-31 the earlier one.
+__global__ void __launch_bounds__(32)
+render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restrict__ tile_order,
                        const uint32_t *__restrict__ point_list,
-                       const float4 *__restrict__ rec, const float4 *__restrict__ cull,
-                       const float *__restrict__ projmatrix, int W, int H, int tiles_x,
-                       const float *__restrict__ final_T,
-                       const uint32_t *__restrict__ n_contrib,
-                       const float *__restrict__ dL_dout, float *__restrict__ dL_dtransMat,
-                       float *__restrict__ dL_dnormal, float *__restrict__ dL_dopacity) {
-  __shared__ float4 s_rec[BW_WARPS][32][4];
-  __shared__ uint32_t s_id[BW_WARPS][32];
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const int x0 = blockIdx.x * SPLAT_TILE + (wid & 1) * SUB_W;
-  const int y0 = blockIdx.y * (2 * SUB_H) + (wid >> 1) * SUB_H;
-  const int px = x0 + (lane & 7), py = y0 + (lane >> 3);
+                       const uint16_t *__restrict__ sub_mask_base, const BinHeader *__restrict__ bhdr,
+                       const float4 *__restrict__ rec, const float *__restrict__ projmatrix, int W,
+                       int H, int tiles_x, uint32_t P, const float *__restrict__ final_T,
+                       const uint32_t *__restrict__ n_contrib, const float *__restrict__ dL_dout,
+                       float *__restrict__ dL_dtransMat, float *__restrict__ dL_dnormal,
+                       float *__restrict__ dL_dopacity) {
+  __shared__ float4 s_rec[2][32][4];
+  __shared__ float s_cut[2][32];
+  __shared__ uint32_t s_pos[2][32];
+  __shared__ uint32_t s_id[2][32];
+  const int lane = threadIdx.x, half = lane >> 4, p16 = lane & 15;
+  const uint32_t work = blockIdx.x;
+  const uint32_t tile = tile_order ? tile_order[work / SUBS_PER_TILE] : work / SUBS_PER_TILE;
+  const int sub = work % SUBS_PER_TILE;
+  const int x0 = (tile % tiles_x) * SPLAT_TILE + (sub & 3) * SUB;
+  const int y0 = (tile / tiles_x) * SPLAT_TILE + (sub >> 2) * SUB;
+  if (x0 >= W || y0 >= H) return;
+  const int px = x0 + (p16 & 3), py = y0 + (p16 >> 2);
   const bool inside = px < W && py < H;
   const size_t HW = (size_t)W * H;
   const size_t pix = (size_t)py * W + px;
 
-  const uint32_t last_contributor = inside ? n_contrib[pix] : 0u;
-  uint32_t max_last = last_contributor;
+  PixelConst pc;
+  pc.last_contributor = inside ? n_contrib[pix] : 0u;
+  uint32_t max_last = pc.last_contributor;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1)
+  for (int o = 8; o > 0; o >>= 1)
     max_last = max(max_last, __shfl_xor_sync(0xffffffffu, max_last, o));
   if (max_last == 0) return;
+  // the forward stored the offset of the mask array in the buffer's header (the capacity it
+  // was laid out with is not known to the backward's caller)
+  const uint16_t *sub_mask = reinterpret_cast<const uint16_t *>(
+      reinterpret_cast<const char *>(sub_mask_base) + bhdr->off_sub_mask);
 
   const float fx = projmatrix[0], fy = projmatrix[5], cx = projmatrix[8], cy = projmatrix[9];
   const PixelRay ray = make_ray((float)px, (float)py, fx, fy, cx, cy);
-  const float inv_period = 1.0f / (6.2831853f * fabsf(fx));
-  const float el_a = fabsf((0.0f - cy) / fy), el_b = fabsf(((float)(H - 1) - cy) / fy);
-  const bool cull_on = fmaxf(el_a, el_b) < 1.55f;
-  const float bx0 = (float)x0, bx1 = (float)(x0 + SUB_W - 1);
-  const float by0 = (float)y0, by1 = (float)(y0 + SUB_H - 1);
-  const uint2 range = ranges[(y0 / SPLAT_TILE) * tiles_x + blockIdx.x];
+  const uint2 range = ranges[tile];
   const uint32_t lt = (1u << lane) - 1u;
 
+  BackState bs;
   const float T_final = inside ? final_T[pix] : 0.0f;
-  float T = T_final;
-  const float final_D = inside ? final_T[pix + HW] : 0.0f;
-  const float final_D2 = inside ? final_T[pix + 2 * HW] : 0.0f;
-  const float final_A = 1.0f - T_final;
-  const uint32_t median_contributor = inside ? n_contrib[pix + HW] : 0u;
-  float gD = 0.f, gA = 0.f, gN0 = 0.f, gN1 = 0.f, gN2 = 0.f, gMed = 0.f, gReg = 0.f;
+  bs.T = T_final;
+  bs.last_dL_dT = bs.accum_depth_rec = bs.accum_alpha_rec = 0.f;
+  bs.accum_n0 = bs.accum_n1 = bs.accum_n2 = 0.f;
+  bs.last_alpha = bs.last_depth = bs.last_n0 = bs.last_n1 = bs.last_n2 = 0.f;
+  pc.final_D = inside ? final_T[pix + HW] : 0.0f;
+  pc.final_D2 = inside ? final_T[pix + 2 * HW] : 0.0f;
+  pc.final_A = 1.0f - T_final;
+  pc.median_contributor = inside ? n_contrib[pix + HW] : 0u;
+  pc.gD = pc.gA = pc.gN0 = pc.gN1 = pc.gN2 = pc.gMed = pc.gReg = 0.f;
   if (inside) {
-    gD = dL_dout[pix];
-    gA = dL_dout[pix + HW];
-    gN0 = dL_dout[pix + 2 * HW];
-    gN1 = dL_dout[pix + 3 * HW];
-    gN2 = dL_dout[pix + 4 * HW];
-    gMed = dL_dout[pix + 5 * HW];
-    gReg = dL_dout[pix + 6 * HW];
+    pc.gD = dL_dout[pix];
+    pc.gA = dL_dout[pix + HW];
+    pc.gN0 = dL_dout[pix + 2 * HW];
+    pc.gN1 = dL_dout[pix + 3 * HW];
+    pc.gN2 = dL_dout[pix + 4 * HW];
+    pc.gMed = dL_dout[pix + 5 * HW];
+    pc.gReg = dL_dout[pix + 6 * HW];
   }
-  float accum_depth_rec = 0.f, accum_alpha_rec = 0.f;
-  float accum_n0 = 0.f, accum_n1 = 0.f, accum_n2 = 0.f;
-  float last_alpha = 0.f, last_depth = 0.f, last_n0 = 0.f, last_n1 = 0.f, last_n2 = 0.f;
-  float last_dL_dT = 0.f;
 
-  for (int chunk = (int)((max_last - 1) >> 5); chunk >= 0; chunk--) {
-    const uint32_t q0 = (uint32_t)chunk << 5;   // 0-based list position of lane 0
-    const uint32_t q = q0 + lane;
-    const bool have = q < max_last;
-    uint32_t id = 0;
-    bool hit = false;
-    if (have) {
-      id = point_list[range.x + q];
-      hit = !cull_on || cull_overlap(cull[id], bx0, bx1, by0, by1, inv_period);
-    }
-    uint32_t m = __ballot_sync(0xffffffffu, hit);
-    if (m == 0) continue;
+  // ---- prologue: stage the top step, fetch masks / indices of the one below ----
+  int chunk = (int)((max_last - 1) >> 5);
+  uint32_t m;
+  {
+    const uint32_t q = ((uint32_t)chunk << 5) + lane;
+    const bool hit = (q < max_last) && ((sub_mask[range.x + q] >> sub) & 1u);
+    m = __ballot_sync(0xffffffffu, hit);
     if (hit) {
       const int slot = __popc(m & lt);
+      const uint32_t id = min(point_list[range.x + q], P - 1u);
       const float4 *r = rec + 4 * (size_t)id;
-      float4 a = __ldg(r), b = __ldg(r + 1), c = __ldg(r + 2), d = __ldg(r + 3);
-      s_rec[wid][slot][0] = a;
-      s_rec[wid][slot][1] = b;
-      s_rec[wid][slot][2] = c;
-      s_rec[wid][slot][3] = d;
-      s_id[wid][slot] = id;
+      const float4 a = __ldg(r), b = __ldg(r + 1), c = __ldg(r + 2), d = __ldg(r + 3);
+      s_rec[0][slot][0] = a; s_rec[0][slot][1] = b; s_rec[0][slot][2] = c; s_rec[0][slot][3] = d;
+      s_cut[0][slot] = rho_cutoff(d.x);
+      s_pos[0][slot] = q;
+      s_id[0][slot] = id;
     }
-    __syncwarp();
-    int slot = __popc(m);
-    while (m) {
-      const int j = 31 - __clz(m);   // back to front
-      m &= ~(1u << j);
-      slot--;
-      const SurfelRec s = unpack_rec(s_rec[wid][slot][0], s_rec[wid][slot][1],
-                                     s_rec[wid][slot][2], s_rec[wid][slot][3]);
-      const uint32_t pos = q0 + j;   // == the reference's `contributor` after decrement
+  }
+  uint32_t nmask = 0u, nid = 0u;
+  if (chunk >= 1) {
+    const uint32_t q = ((uint32_t)(chunk - 1) << 5) + lane;
+    nmask = sub_mask[range.x + q];
+    nid = point_list[range.x + q];
+  }
+  __syncwarp();
+  const uint32_t hmask = half ? 0xffff0000u : 0x0000ffffu;
+  int cur = 0;
+  for (; chunk >= 0; chunk--, cur ^= 1) {
+    // ---- issue the loads of the step below ----
+    const bool nhit = (chunk >= 1) && ((nmask >> sub) & 1u);
+    const uint32_t nm = __ballot_sync(0xffffffffu, nhit);
+    const uint32_t id1 = min(nid, P - 1u);
+    if (chunk >= 2) {
+      const uint32_t q = ((uint32_t)(chunk - 2) << 5) + lane;
+      nmask = sub_mask[range.x + q];
+      nid = point_list[range.x + q];
+    }
+    float4 na, nb, nc, nd;
+    if (nhit) {
+      const float4 *r = rec + 4 * (size_t)id1;
+      na = __ldg(r); nb = __ldg(r + 1); nc = __ldg(r + 2); nd = __ldg(r + 3);
+    }
+    // ---- this step's survivors, back to front, two at a time ----
+    const int nsurv = __popc(m);
+    for (int top = nsurv - 1; top >= 0; top -= 2) {
+      // lanes 0-15 take survivor `top` (later in the list), lanes 16-31 survivor `top - 1`
+      const int slot = top - half;
+      const bool mine = slot >= 0;
+      const int sl = mine ? slot : top;
+      const SurfelRec s = unpack_rec(s_rec[cur][sl][0], s_rec[cur][sl][1], s_rec[cur][sl][2],
+                                     s_rec[cur][sl][3]);
+      const uint32_t pos = s_pos[cur][sl];   // == the reference's `contributor` after decrement
+      Hit h;
+      const bool maybe = mine && pos < pc.last_contributor && intersect_begin(ray, s, s_cut[cur][sl], h);
+      if (!__any_sync(0xffffffffu, maybe)) continue;
+      const bool ok = maybe && intersect_finish(ray, s, h);
+      const bool ok_o = __shfl_xor_sync(0xffffffffu, (int)ok, 16) != 0;
+      const float alpha_o = __shfl_xor_sync(0xffffffffu, h.alpha, 16);
+      const float depth_o = __shfl_xor_sync(0xffffffffu, h.depth, 16);
+      const bool ok1 = half ? ok_o : ok, ok2 = half ? ok : ok_o;
+      StepOut o1, o2;
+      o1.T = o1.w = o1.dL_dalpha = o1.dLd_depth = 0.f;
+      o2 = o1;
+      if (ok1) {
+        const float4 c = s_rec[cur][top][2];
+        o1 = recur(bs, pc, half ? alpha_o : h.alpha, half ? depth_o : h.depth, c.y, c.z, c.w,
+                   s_pos[cur][top]);
+      }
+      if (ok2) {
+        const float4 c = s_rec[cur][top - 1][2];
+        o2 = recur(bs, pc, half ? h.alpha : alpha_o, half ? h.depth : depth_o, c.y, c.z, c.w,
+                   s_pos[cur][top - 1]);
+      }
+      // each half finishes the gradient of ITS surfel
+      if ((__ballot_sync(0xffffffffu, ok) & hmask) == 0u) continue;
+      const StepOut o = half ? o2 : o1;
       float v[16];
 #pragma unroll
       for (int i = 0; i < 16; i++) v[i] = 0.0f;
-      bool contributes = false;
-      Hit h;
-      if (pos < last_contributor && intersect(ray, s, h)) {
-        contributes = true;
-        const float alpha = h.alpha, depth = h.depth;
-        T = __fdiv_rn(T, 1.0f - alpha);
-        const float w = alpha * T;
-        const float dL_dweight =
-            (final_D2 + depth * depth * final_A - 2.0f * depth * final_D) * gReg;
-        float dL_dalpha = dL_dweight - last_dL_dT;
-        last_dL_dT = dL_dweight * alpha + (1.0f - alpha) * last_dL_dT;
-        float dLd_depth = 2.0f * (T * alpha) * (depth * final_A - final_D) * gReg;
-        if (pos == median_contributor - 1u) dLd_depth += gMed;
-        dLd_depth += w * gD;
-        accum_depth_rec = last_alpha * last_depth + (1.0f - last_alpha) * accum_depth_rec;
-        last_depth = depth;
-        dL_dalpha += (depth - accum_depth_rec) * gD;
-        accum_n0 = last_alpha * last_n0 + (1.0f - last_alpha) * accum_n0;
-        accum_n1 = last_alpha * last_n1 + (1.0f - last_alpha) * accum_n1;
-        accum_n2 = last_alpha * last_n2 + (1.0f - last_alpha) * accum_n2;
-        last_n0 = s.nx; last_n1 = s.ny; last_n2 = s.nz;
-        dL_dalpha += (s.nx - accum_n0) * gN0;
-        dL_dalpha += (s.ny - accum_n1) * gN1;
-        dL_dalpha += (s.nz - accum_n2) * gN2;
-        v[9] = w * gN0;
-        v[10] = w * gN1;
-        v[11] = w * gN2;
-        accum_alpha_rec = last_alpha + (1.0f - last_alpha) * accum_alpha_rec;
-        dL_dalpha += (1.0f - accum_alpha_rec) * gA;
-        dL_dalpha *= T;
-        last_alpha = alpha;
+      if (ok) {
+        const float alpha = h.alpha, depth = h.depth, T = o.T, dL_dalpha = o.dL_dalpha,
+                    dLd_depth = o.dLd_depth;
+        v[9] = o.w * pc.gN0;
+        v[10] = o.w * pc.gN1;
+        v[11] = o.w * pc.gN2;
         v[12] = h.G * dL_dalpha;   // Q1: the 0.99 clamp is ignored here
         if (h.rho3d <= h.rho2d) {
           const float inv_depth = 1.0f / depth;
@@ -177,8 +251,7 @@ render_backward_kernel(const uint2 *__restrict__ ranges,
           const float ddx = c2 * h.dx, ddy = c2 * h.dy;
           const float ss = s.twx * s.twx + s.twy * s.twy;
           const float sn = sqrtf(ss);
-          const float inv_ss = 1.0f / ss, inv_snd = 1.0f / (sn * s.d2d),
-                      inv_d2d = 1.0f / s.d2d;
+          const float inv_ss = 1.0f / ss, inv_snd = 1.0f / (sn * s.d2d), inv_d2d = 1.0f / s.d2d;
           const float gx = fx * ddx, gy = fy * ddy;
           const float cw = dLd_depth * inv_d2d;
           v[6] = gx * (-s.twy * inv_ss) + gy * (-s.twx * s.twz * inv_snd) + cw * s.twx;
@@ -186,48 +259,55 @@ render_backward_kernel(const uint2 *__restrict__ ranges,
           v[8] = gy * sn * inv_d2d + cw * s.twz;
         }
       }
-      if (__ballot_sync(0xffffffffu, contributes) == 0u) continue;
-      // transposed butterfly: 16 values x 32 lanes -> lane l holds the total of v[l>>1]
+      // transposed butterfly inside the half warp: 16 values x 16 lanes -> lane p holds v[p]
       {
-        const bool hi = lane & 16;
+        const bool hi = p16 & 8;
 #pragma unroll
         for (int i = 0; i < 8; i++) {
           float send = hi ? v[i] : v[i + 8], keep = hi ? v[i + 8] : v[i];
-          v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+          v[i] = keep + __shfl_xor_sync(hmask, send, 8);
         }
       }
       {
-        const bool hi = lane & 8;
+        const bool hi = p16 & 4;
 #pragma unroll
         for (int i = 0; i < 4; i++) {
           float send = hi ? v[i] : v[i + 4], keep = hi ? v[i + 4] : v[i];
-          v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+          v[i] = keep + __shfl_xor_sync(hmask, send, 4);
         }
       }
       {
-        const bool hi = lane & 4;
+        const bool hi = p16 & 2;
 #pragma unroll
         for (int i = 0; i < 2; i++) {
           float send = hi ? v[i] : v[i + 2], keep = hi ? v[i + 2] : v[i];
-          v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+          v[i] = keep + __shfl_xor_sync(hmask, send, 2);
         }
       }
       {
-        const bool hi = lane & 2;
+        const bool hi = p16 & 1;
         float send = hi ? v[0] : v[1], keep = hi ? v[1] : v[0];
-        v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+        v[0] = keep + __shfl_xor_sync(hmask, send, 1);
       }
-      v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
-      const int comp = lane >> 1;
-      if ((lane & 1) == 0 && comp <= 12 && v[0] != 0.0f) {
-        const size_t gid = s_id[wid][slot];
+      if (p16 <= 12 && v[0] != 0.0f) {
+        const size_t gid = s_id[cur][sl];
         float *dst;
-        if (comp < 9) dst = dL_dtransMat + gid * 12 + (comp / 3) * 4 + (comp % 3);
-        else if (comp < 12) dst = dL_dnormal + gid * 3 + (comp - 9);
+        if (p16 < 9) dst = dL_dtransMat + gid * 12 + (p16 / 3) * 4 + (p16 % 3);
+        else if (p16 < 12) dst = dL_dnormal + gid * 3 + (p16 - 9);
         else dst = dL_dopacity + gid;
         atomicAdd(dst, v[0]);
       }
     }
+    // ---- park the records of the step below in the other buffer ----
+    if (nhit) {
+      const int slot = __popc(nm & lt);
+      s_rec[cur ^ 1][slot][0] = na; s_rec[cur ^ 1][slot][1] = nb;
+      s_rec[cur ^ 1][slot][2] = nc; s_rec[cur ^ 1][slot][3] = nd;
+      s_cut[cur ^ 1][slot] = rho_cutoff(nd.x);
+      s_pos[cur ^ 1][slot] = ((uint32_t)(chunk - 1) << 5) + lane;
+      s_id[cur ^ 1][slot] = id1;
+    }
+    m = nm;
     __syncwarp();
   }
 }
@@ -312,10 +392,10 @@ backward_preprocess_kernel(int P, const int *__restrict__ radii,
 
 void launch_render_backward(const BwdParams &p, const GeomView &g, const ImageView &im,
                             const BinView &b, cudaStream_t s) {
-  dim3 grid(im.tiles_x, (p.H + 2 * SUB_H - 1) / (2 * SUB_H));
-  render_backward_kernel<<<grid, BW_WARPS * 32, 0, s>>>(
-      im.ranges, b.point_list, g.rec, g.cull, p.projmatrix, p.W, p.H, im.tiles_x,
-      im.final_T, im.n_contrib, p.dL_dout, p.dL_dtransMat, p.dL_dnormal, p.dL_dopacity);
+  render_backward_kernel<<<im.tiles * SUBS_PER_TILE, 32, 0, s>>>(
+      im.ranges, im.tile_order, b.point_list, reinterpret_cast<const uint16_t *>(b.hdr), b.hdr,
+      g.rec, p.projmatrix, p.W, p.H, im.tiles_x, (uint32_t)p.P, im.final_T, im.n_contrib,
+      p.dL_dout, p.dL_dtransMat, p.dL_dnormal, p.dL_dopacity);
 }
 
 void launch_backward_preprocess(const BwdParams &p, cudaStream_t s) {

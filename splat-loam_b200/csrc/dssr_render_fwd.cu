@@ -5,152 +5,205 @@
 //
 // The reference runs one 256-thread CTA per 16x16 tile; every pixel walks the tile's
 // whole depth-sorted list and the CTA leaves only when all 256 pixels are done.  On a
-// 64x1024 range image that is 256 CTAs on 148 SMs.  Here the unit of work is a WARP
-// that owns an 8x4 pixel sub-tile and walks its tile's list on its own:
-//   * 32 list entries are fetched per step (one per lane, coalesced), each lane tests
-//     its entry's conservative cull box against the sub-tile, a ballot compacts the
-//     survivors, whose 64-byte records are gathered (128-bit loads, L2-resident) into
-//     a warp-private shared-memory ring;
-//   * the survivors are then composited in list order by all 32 pixels;
-//   * the warp stops as soon as ITS 32 pixels are done.
-// Skipping an entry whose cull box misses the sub-tile is exact: such an entry fails
-// the reference's alpha >= 1/255 test at every pixel of the sub-tile, i.e. it is one
-// the reference `continue`s over without touching any state.  `contributor` keeps
-// counting list positions, so n_contrib / median_contributor are the reference's.
+// 64x1024 range image that is 256 CTAs on 148 SMs, and a warp's dependent-instruction
+// chain is as long as the tile's list.  Here the unit of work is a WARP that owns a 4x4
+// pixel sub-tile (4096 warps at 64x1024) and walks its tile's list on its own:
+//   * 32 list entries per step: each lane reads its entry's 16-bit sub-tile mask (written
+//     by the last sort pass from the surfel's conservative cull box) and a ballot compacts
+//     the entries that can touch this sub-tile; their 64-byte records are gathered
+//     (128-bit loads, L2-resident) into a warp-private shared-memory ring;
+//   * survivors are evaluated TWO AT A TIME: lanes 0-15 intersect the 16 pixels with one
+//     surfel, lanes 16-31 with the next; the results are swapped by shuffle and both
+//     halves blend both surfels in list order, so every lane carries its pixel's state;
+//   * the warp stops as soon as ITS 16 pixels are done.
+// Skipping an entry whose cull box misses the sub-tile is exact: such an entry fails the
+// reference's alpha >= 1/255 test at every pixel of the sub-tile, i.e. it is one the
+// reference `continue`s over without touching any state.  `contributor` keeps counting
+// list positions, so n_contrib / median_contributor are the reference's.
+#include <cstdlib>
+
 #include "raster_math.cuh"
 
 namespace {
 
-constexpr int FW_WARPS = 4;            // warps per CTA: a 16x8 pixel half tile
-constexpr int SUB_W = 8, SUB_H = 4;    // pixels per warp
+constexpr int SUB = 4;                                            // 4x4 pixels per warp
+constexpr int SUBS_PER_TILE = (SPLAT_TILE / SUB) * (SPLAT_TILE / SUB);   // 16
 
-__global__ void __launch_bounds__(FW_WARPS * 32)
-render_forward_kernel(const uint2 *__restrict__ ranges,
+struct PixelState {
+  float T, D, N0, N1, N2, M1, M2, dist, median_depth;
+  uint32_t last_contributor, median_contributor;
+  bool done;
+};
+
+// forward.cu:302-330 for one surviving (pixel, surfel) pair
+__device__ __forceinline__ void blend(PixelState &p, float alpha, float depth, float nx, float ny,
+                                      float nz, uint32_t contributor) {
+  const float test_T = FM(p.T, FS(1.0f, alpha));
+  if (test_T < 0.0001f) {
+    p.done = true;
+    return;
+  }
+  const float w = FM(p.T, alpha);
+  const float A = FS(1.0f, p.T);
+  const float mm = FM(depth, depth), m2 = FA(depth, depth);
+  float tmp = FF(A, mm, p.M2);
+  tmp = FF(-p.M1, m2, tmp);
+  p.dist = FF(w, tmp, p.dist);
+  p.M2 = FF(w, mm, p.M2);
+  p.M1 = FF(depth, w, p.M1);
+  p.D = FF(depth, w, p.D);
+  if (p.T > 0.5f) {
+    p.median_depth = depth;
+    p.median_contributor = contributor;
+  }
+  p.N0 = FF(nx, w, p.N0);
+  p.N1 = FF(ny, w, p.N1);
+  p.N2 = FF(nz, w, p.N2);
+  p.T = test_T;
+  p.last_contributor = contributor;
+}
+
+// One WARP per CTA = one 4x4 sub-tile.  CTAs are numbered in order of decreasing tile list
+// length (tile_order), so the hardware's round-robin placement hands every SM a balanced
+// mix of long and short lists.
+__global__ void __launch_bounds__(32)
+render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restrict__ tile_order,
                       const uint32_t *__restrict__ point_list,
-                      const float4 *__restrict__ rec, const float4 *__restrict__ cull,
+                      const uint16_t *__restrict__ sub_mask, const float4 *__restrict__ rec,
                       const float *__restrict__ projmatrix, int W, int H, int tiles_x,
                       uint32_t capacity, uint32_t P, float *__restrict__ final_T,
-                      uint32_t *__restrict__ n_contrib,
-                      float *__restrict__ out) {
-  __shared__ float4 s_rec[FW_WARPS][32][4];
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const int x0 = blockIdx.x * SPLAT_TILE + (wid & 1) * SUB_W;
-  const int y0 = blockIdx.y * (2 * SUB_H) + (wid >> 1) * SUB_H;
-  const int px = x0 + (lane & 7), py = y0 + (lane >> 3);
+                      uint32_t *__restrict__ n_contrib, float *__restrict__ out) {
+  // double-buffered staging ring: while the survivors of one 32-entry step are being
+  // composited, the records of the next step's survivors are already in flight
+  __shared__ float4 s_rec[2][32][4];
+  __shared__ float s_cut[2][32];
+  __shared__ uint32_t s_pos[2][32];
+  const int lane = threadIdx.x, half = lane >> 4, p16 = lane & 15;
+  const uint32_t work = blockIdx.x;
+  const uint32_t tile = tile_order ? tile_order[work / SUBS_PER_TILE] : work / SUBS_PER_TILE;
+  const int sub = work % SUBS_PER_TILE;
+  const int x0 = (tile % tiles_x) * SPLAT_TILE + (sub & 3) * SUB;
+  const int y0 = (tile / tiles_x) * SPLAT_TILE + (sub >> 2) * SUB;
+  if (x0 >= W || y0 >= H) return;
+  const int px = x0 + (p16 & 3), py = y0 + (p16 >> 2);
   const bool inside = px < W && py < H;
   const float fx = projmatrix[0], fy = projmatrix[5], cx = projmatrix[8], cy = projmatrix[9];
   const PixelRay ray = make_ray((float)px, (float)py, fx, fy, cx, cy);
-  const float inv_period = 1.0f / (6.2831853f * fabsf(fx));
-  // culling assumes |elevation| < pi/2 on every image row
-  const float el_a = fabsf((0.0f - cy) / fy), el_b = fabsf(((float)(H - 1) - cy) / fy);
-  const bool cull_on = fmaxf(el_a, el_b) < 1.55f;
-  const float bx0 = (float)x0, bx1 = (float)(x0 + SUB_W - 1);
-  const float by0 = (float)y0, by1 = (float)(y0 + SUB_H - 1);
 
-  uint2 range = ranges[(y0 / SPLAT_TILE) * tiles_x + blockIdx.x];
+  uint2 range = ranges[tile];
   range.x = min(range.x, capacity);   // only bites when the capacity hint was too small
   range.y = min(range.y, capacity);
   const uint32_t lt = (1u << lane) - 1u;
 
-  float T = 1.0f, D = 0.0f, N0 = 0.0f, N1 = 0.0f, N2 = 0.0f, M1 = 0.0f, M2 = 0.0f;
-  float dist = 0.0f, median_depth = 0.0f;
-  uint32_t last_contributor = 0, median_contributor = 0;
-  bool done = !inside;
+  PixelState ps;
+  ps.T = 1.0f;
+  ps.D = ps.N0 = ps.N1 = ps.N2 = ps.M1 = ps.M2 = ps.dist = ps.median_depth = 0.0f;
+  ps.last_contributor = ps.median_contributor = 0;
+  ps.done = !inside;
 
-  // software prefetch of the next 32 entries
-  uint32_t nid = 0;
-  float4 ncb = make_float4(0.f, 0.f, 0.f, 0.f);
-  // (id < P only fails on the garbage a too-small capacity hint leaves behind; that
-  // frame is re-run with the exact size)
-  bool nhave = range.x + lane < range.y;
-  if (nhave) {
-    nid = point_list[range.x + lane];
-    nhave = nid < P;
-    if (nhave) ncb = cull[nid];
-  }
-  for (uint32_t base = range.x; base < range.y; base += 32) {
-    if (__all_sync(0xffffffffu, done)) break;
-    const uint32_t id = nid;
-    const float4 cb = ncb;
-    const bool have = nhave;
-    {
-      uint32_t ni = base + 32 + lane;
-      nhave = ni < range.y;
-      if (nhave) {
-        nid = point_list[ni];
-        nhave = nid < P;
-        if (nhave) ncb = cull[nid];
-      }
-    }
-    const bool hit = have && (!cull_on || cull_overlap(cb, bx0, bx1, by0, by1, inv_period));
-    uint32_t m = __ballot_sync(0xffffffffu, hit);
-    if (m == 0) continue;
+  // ---- prologue: stage step 0, fetch the masks of step 1 ----
+  uint32_t m;   // survivors of the step about to be composited (staged in buffer `cur`)
+  {
+    const uint32_t i0 = range.x + lane;
+    const bool hit = (i0 < range.y) && ((sub_mask[i0] >> sub) & 1u);
+    m = __ballot_sync(0xffffffffu, hit);
     if (hit) {
       const int slot = __popc(m & lt);
+      // (id < P only fails on the garbage a too-small capacity hint leaves behind; that
+      // frame is re-run with the exact size)
+      const uint32_t id = min(point_list[i0], P - 1u);
       const float4 *r = rec + 4 * (size_t)id;
-      float4 a = __ldg(r), b = __ldg(r + 1), c = __ldg(r + 2), d = __ldg(r + 3);
-      s_rec[wid][slot][0] = a;
-      s_rec[wid][slot][1] = b;
-      s_rec[wid][slot][2] = c;
-      s_rec[wid][slot][3] = d;
+      const float4 a = __ldg(r), b = __ldg(r + 1), c = __ldg(r + 2), d = __ldg(r + 3);
+      s_rec[0][slot][0] = a; s_rec[0][slot][1] = b; s_rec[0][slot][2] = c; s_rec[0][slot][3] = d;
+      s_cut[0][slot] = rho_cutoff(d.x);
+      s_pos[0][slot] = lane + 1;   // the reference's `contributor`
     }
-    __syncwarp();
-    int slot = 0;
-    while (m) {
-      const int j = __ffs(m) - 1;
-      m &= m - 1;
-      const SurfelRec s = unpack_rec(s_rec[wid][slot][0], s_rec[wid][slot][1],
-                                     s_rec[wid][slot][2], s_rec[wid][slot][3]);
-      slot++;
-      if (!done) {
-        Hit h;
-        if (intersect(ray, s, h)) {
-          const uint32_t contributor = base - range.x + j + 1;
-          const float test_T = FM(T, FS(1.0f, h.alpha));
-          if (test_T < 0.0001f) {
-            done = true;
-          } else {
-            const float w = FM(T, h.alpha);
-            const float A = FS(1.0f, T);
-            const float mm = FM(h.depth, h.depth), m2 = FA(h.depth, h.depth);
-            float tmp = FF(A, mm, M2);
-            tmp = FF(-M1, m2, tmp);
-            dist = FF(w, tmp, dist);
-            M2 = FF(w, mm, M2);
-            M1 = FF(h.depth, w, M1);
-            D = FF(h.depth, w, D);
-            if (T > 0.5f) {
-              median_depth = h.depth;
-              median_contributor = contributor;
-            }
-            N0 = FF(s.nx, w, N0);
-            N1 = FF(s.ny, w, N1);
-            N2 = FF(s.nz, w, N2);
-            T = test_T;
-            last_contributor = contributor;
-          }
-        }
+  }
+  // masks and surfel indices run two steps ahead, records one step ahead
+  uint32_t nmask = 0u, nid = 0u;
+  if (range.x + 32 + lane < range.y) {
+    nmask = sub_mask[range.x + 32 + lane];
+    nid = point_list[range.x + 32 + lane];
+  }
+  __syncwarp();
+  int cur = 0;
+  for (uint32_t base = range.x; base < range.y; base += 32, cur ^= 1) {
+    if (__all_sync(0xffffffffu, ps.done)) break;
+    // ---- issue the loads of the NEXT step (consumed after this step's compositing) ----
+    const bool nhit = (nmask >> sub) & 1u;
+    const uint32_t nm = __ballot_sync(0xffffffffu, nhit);
+    const uint32_t id1 = min(nid, P - 1u);
+    {
+      const uint32_t ni = base + 64 + lane;
+      nmask = 0u;
+      if (ni < range.y) {
+        nmask = sub_mask[ni];
+        nid = point_list[ni];
       }
-      if (__all_sync(0xffffffffu, done)) break;
     }
+    float4 na, nb, nc, nd;
+    if (nhit) {
+      const float4 *r = rec + 4 * (size_t)id1;
+      na = __ldg(r); nb = __ldg(r + 1); nc = __ldg(r + 2); nd = __ldg(r + 3);
+    }
+    // ---- composite this step's survivors, two at a time ----
+    const int nsurv = __popc(m);
+    for (int pair = 0; pair < nsurv; pair += 2) {
+      // lanes 0-15 take survivor `pair`, lanes 16-31 survivor `pair + 1`
+      const int slot = pair + half;
+      const bool mine = slot < nsurv;
+      const int sl = mine ? slot : pair;
+      const SurfelRec s = unpack_rec(s_rec[cur][sl][0], s_rec[cur][sl][1], s_rec[cur][sl][2],
+                                     s_rec[cur][sl][3]);
+      Hit h;
+      const bool maybe = mine && !ps.done && intersect_begin(ray, s, s_cut[cur][sl], h);
+      // the cull box is only a box: skip the expensive half when no pixel can pass
+      if (!__any_sync(0xffffffffu, maybe)) continue;
+      const bool ok = maybe && intersect_finish(ray, s, h);
+      // swap results between the halves: every lane gets (first, second) for its pixel
+      const bool ok_o = __shfl_xor_sync(0xffffffffu, (int)ok, 16) != 0;
+      const float alpha_o = __shfl_xor_sync(0xffffffffu, h.alpha, 16);
+      const float depth_o = __shfl_xor_sync(0xffffffffu, h.depth, 16);
+      const bool ok1 = half ? ok_o : ok, ok2 = half ? ok : ok_o;
+      if (ok1) {
+        const float4 c = s_rec[cur][pair][2];
+        blend(ps, half ? alpha_o : h.alpha, half ? depth_o : h.depth, c.y, c.z, c.w,
+              s_pos[cur][pair]);
+      }
+      if (ok2 && !ps.done) {
+        const float4 c = s_rec[cur][pair + 1][2];
+        blend(ps, half ? h.alpha : alpha_o, half ? h.depth : depth_o, c.y, c.z, c.w,
+              s_pos[cur][pair + 1]);
+      }
+      if (__all_sync(0xffffffffu, ps.done)) break;
+    }
+    // ---- park the next step's records in the other buffer ----
+    if (nhit) {
+      const int slot = __popc(nm & lt);
+      s_rec[cur ^ 1][slot][0] = na; s_rec[cur ^ 1][slot][1] = nb;
+      s_rec[cur ^ 1][slot][2] = nc; s_rec[cur ^ 1][slot][3] = nd;
+      s_cut[cur ^ 1][slot] = rho_cutoff(nd.x);
+      s_pos[cur ^ 1][slot] = base - range.x + 32 + lane + 1;
+    }
+    m = nm;
     __syncwarp();
   }
 
-  if (inside) {
+  if (inside && half == 0) {
     const size_t HW = (size_t)W * H;
     const size_t pix = (size_t)py * W + px;
-    final_T[pix] = T;
-    final_T[pix + HW] = M1;
-    final_T[pix + 2 * HW] = M2;
-    n_contrib[pix] = last_contributor;
-    n_contrib[pix + HW] = median_contributor;
-    out[pix] = D;                      // DEPTH_OFFSET
-    out[pix + HW] = FS(1.0f, T);       // ALPHA_OFFSET
-    out[pix + 2 * HW] = N0;            // NORMAL_OFFSET..+2
-    out[pix + 3 * HW] = N1;
-    out[pix + 4 * HW] = N2;
-    out[pix + 5 * HW] = median_depth;  // MIDDEPTH_OFFSET
-    out[pix + 6 * HW] = dist;          // DISTORTION_OFFSET
+    final_T[pix] = ps.T;
+    final_T[pix + HW] = ps.M1;
+    final_T[pix + 2 * HW] = ps.M2;
+    n_contrib[pix] = ps.last_contributor;
+    n_contrib[pix + HW] = ps.median_contributor;
+    out[pix] = ps.D;                      // DEPTH_OFFSET
+    out[pix + HW] = FS(1.0f, ps.T);       // ALPHA_OFFSET
+    out[pix + 2 * HW] = ps.N0;            // NORMAL_OFFSET..+2
+    out[pix + 3 * HW] = ps.N1;
+    out[pix + 4 * HW] = ps.N2;
+    out[pix + 5 * HW] = ps.median_depth;  // MIDDEPTH_OFFSET
+    out[pix + 6 * HW] = ps.dist;          // DISTORTION_OFFSET
   }
 }
 
@@ -158,8 +211,17 @@ render_forward_kernel(const uint2 *__restrict__ ranges,
 
 void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageView &im,
                            const BinView &b, uint32_t capacity, cudaStream_t s) {
-  dim3 grid(im.tiles_x, (p.H + 2 * SUB_H - 1) / (2 * SUB_H));
-  render_forward_kernel<<<grid, FW_WARPS * 32, 0, s>>>(
-      im.ranges, b.point_list, g.rec, g.cull, p.projmatrix, p.W, p.H, im.tiles_x,
-      capacity, (uint32_t)p.P, im.final_T, im.n_contrib, p.out_maps);
+  // experiment knob: extra dynamic shared memory per CTA limits how many warps are resident
+  // per SM, turning the launch into several dynamically scheduled waves
+  static int extra_smem = -1;
+  if (extra_smem < 0) {
+    const char *e = getenv("SPLAT_FWD_SMEM");
+    extra_smem = e ? atoi(e) : 0;
+    if (extra_smem > 48 * 1024)
+      cudaFuncSetAttribute(render_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           extra_smem);
+  }
+  render_forward_kernel<<<im.tiles * SUBS_PER_TILE, 32, extra_smem, s>>>(
+      im.ranges, im.tile_order, b.point_list, b.sub_mask, g.rec, p.projmatrix, p.W, p.H,
+      im.tiles_x, capacity, (uint32_t)p.P, im.final_T, im.n_contrib, p.out_maps);
 }

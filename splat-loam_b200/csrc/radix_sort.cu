@@ -17,7 +17,7 @@
 // tile (two when there are more than 1024 tiles) — 4 passes of 8 B/instance instead
 // of CUB's 6 passes of 12 B/instance.  The last pass unpacks to the reference's
 // point_list_keys (u64) and point_list (u32), which are therefore bit-identical.
-#include "common.cuh"
+#include "raster_math.cuh"
 
 namespace {
 
@@ -91,13 +91,30 @@ __global__ void identify_ranges_kernel(const uint32_t *num_ptr, uint32_t capacit
   if (i == L - 1) ranges[cur].y = L;
 }
 
+// tile_order[rank] = tile, rank by decreasing list length (ties by index): the compositing
+// kernels number their CTAs through it so that long and short lists are spread evenly.
+__global__ void tile_order_kernel(const uint2 *__restrict__ ranges, int tiles,
+                                  uint32_t *tile_order) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= tiles) return;
+  const uint2 me = ranges[t];
+  const uint32_t len = me.y - me.x;
+  uint32_t rank = 0;
+  for (int o = 0; o < tiles; o++) {
+    const uint2 r = ranges[o];
+    const uint32_t l = r.y - r.x;
+    rank += (l > len) || (l == len && o < t);
+  }
+  tile_order[rank] = (uint32_t)t;
+}
+
 // One radix pass.  Each CTA takes a ticket (so CTA b only ever waits on CTAs that
 // have already started), ranks its 4096 words stably per digit with warp match-any,
 // publishes its digit counts, resolves its global offsets by looking back over the
 // predecessors' published counts, and scatters.
 __global__ void __launch_bounds__(SORT_THREADS)
 sort_pass_kernel(const unsigned long long *__restrict__ in, unsigned long long *out,
-                 unsigned long long *keys_out, uint32_t *plist_out,
+                 unsigned long long *keys_out, uint32_t *plist_out, MaskParams mp,
                  const uint32_t *__restrict__ num_ptr, uint32_t capacity, uint32_t *status,
                  uint32_t *ticket, const uint32_t *__restrict__ digit_base, int shift,
                  int bits, int last, int idx_bits) {
@@ -178,6 +195,14 @@ sort_pass_kernel(const unsigned long long *__restrict__ in, unsigned long long *
   __syncthreads();
 
   const unsigned long long idx_mask = (1ull << idx_bits) - 1ull;
+  float inv_period = 0.0f;
+  bool cull_on = false;
+  if (last && mp.sub_mask) {
+    const float fx = mp.projmatrix[0], fy = mp.projmatrix[5], cy = mp.projmatrix[9];
+    inv_period = 1.0f / (6.2831853f * fabsf(fx));
+    // culling assumes |elevation| < pi/2 on every image row
+    cull_on = fmaxf(fabsf((0.0f - cy) / fy), fabsf(((float)(mp.H - 1) - cy) / fy)) < 1.55f;
+  }
 #pragma unroll
   for (int r = 0; r < SORT_ITEMS; r++) {
     uint32_t i = wstart + r * 32 + lane;
@@ -192,6 +217,15 @@ sort_pass_kernel(const unsigned long long *__restrict__ in, unsigned long long *
         unsigned long long tile = k >> (idx_bits + SPLAT_DEPTH_BITS);
         keys_out[pos] = (tile << 32) | (unsigned long long)(d27 + SPLAT_DEPTH_BASE);
         plist_out[pos] = idx;
+        if (mp.sub_mask) {
+          uint32_t sm = 0xffffu;
+          if (cull_on) {
+            const uint32_t t = (uint32_t)tile;
+            sm = subtile_mask(mp.cull[idx], (float)((t % mp.tiles_x) * SPLAT_TILE),
+                              (float)((t / mp.tiles_x) * SPLAT_TILE), inv_period);
+          }
+          mp.sub_mask[pos] = (uint16_t)sm;
+        }
       } else {
         out[pos] = key[r];
       }
@@ -212,6 +246,7 @@ void launch_digit_scan(const uint32_t *hist, uint32_t *digit_base, int npass, ui
 // Returns the array that holds the sorted words otherwise.
 unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long *b,
                                        unsigned long long *keys_out, uint32_t *plist_out,
+                                       MaskParams mp,
                                        const uint32_t *num_ptr, uint32_t capacity,
                                        uint32_t *status, const size_t *status_off,
                                        uint32_t *tickets, const uint32_t *digit_base,
@@ -224,7 +259,7 @@ unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long
     const size_t smem = (size_t)WARPS * nbins * 2 + (size_t)nbins * 4;
     const int last = unpack_last && (p == npass - 1);
     sort_pass_kernel<<<nblk, SORT_THREADS, smem, s>>>(
-        src, dst, keys_out, plist_out, num_ptr, capacity, status + status_off[p],
+        src, dst, keys_out, plist_out, mp, num_ptr, capacity, status + status_off[p],
         tickets + p, digit_base + p * SORT_MAX_BINS, shift[p], bits[p], last, idx_bits);
     unsigned long long *t = dst;
     dst = src;
@@ -233,11 +268,17 @@ unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long
   return src;
 }
 
-void launch_sort(const GeomView &g, const ImageView &im, const BinView &b,
+void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, const BinView &b,
                  const SortPlan &sp, uint32_t capacity, cudaStream_t s) {
+  MaskParams mp;
+  mp.sub_mask = b.sub_mask;
+  mp.cull = g.cull;
+  mp.projmatrix = p.projmatrix;
+  mp.tiles_x = im.tiles_x;
+  mp.H = p.H;
   const int single = (sp.npass == 4) ? 3 : -1;
   launch_digit_scan(b.hist, b.digit_base, sp.npass, im.ranges, im.tiles, single, HIST_REPL, s);
-  launch_sort_passes(b.words_a, b.words_b, b.keys, b.point_list, &g.hdr->num_rendered,
+  launch_sort_passes(b.words_a, b.words_b, b.keys, b.point_list, mp, &g.hdr->num_rendered,
                      capacity, b.status, b.status_off, b.tickets, b.digit_base, sp.npass,
                      sp.shift, sp.bits, 1, sp.idx_bits, b.nblk, s);
   if (single < 0) {
@@ -247,4 +288,5 @@ void launch_sort(const GeomView &g, const ImageView &im, const BinView &b,
       identify_ranges_kernel<<<blocks, 256, 0, s>>>(&g.hdr->num_rendered, capacity, b.keys,
                                                     im.ranges);
   }
+  tile_order_kernel<<<(im.tiles + 127) / 128, 128, 0, s>>>(im.ranges, im.tiles, im.tile_order);
 }

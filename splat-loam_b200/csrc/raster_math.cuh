@@ -63,8 +63,20 @@ struct Hit {
   float depth, G, alpha;
 };
 
-// Returns false when the reference would `continue` (forward.cu:271-301).
-__device__ __forceinline__ bool intersect(const PixelRay &r, const SurfelRec &s, Hit &h) {
+// Conservative cutoff on rho = min(rho3d, rho2d): beyond it alpha = min(0.99, opa *
+// exp(-rho/2)) is below 1/255 with a 0.4 % margin (far above any rounding of the exact
+// evaluation).  Same formula as the cull box of the preprocess kernel.
+__device__ __forceinline__ float rho_cutoff(float opa) {
+  return 2.0f * logf(255.0f * opa) * 1.002f + 0.01f;
+}
+
+// First half of the evaluation: the transformed planes, their cross product and the
+// pixel-space distance (forward.cu:265-277).  Returns false when this lane provably ends in
+// one of the reference's `continue`s: p.z == 0, or both rho3d = |p.xy|^2 / p.z^2 and rho2d
+// exceed the surfel's cutoff, i.e. alpha < 1/255.  The test uses the very floats the exact
+// evaluation goes on with; NaNs compare false and fall through to the exact path.
+__device__ __forceinline__ bool intersect_begin(const PixelRay &r, const SurfelRec &s, float cut,
+                                                Hit &h) {
   h.kx = FF(0.0f, s.tuz, FF(s.tux, r.ax, FM(s.tuy, r.ay)));
   h.ky = FF(0.0f, s.tvz, FF(s.tvx, r.ax, FM(s.tvy, r.ay)));
   h.kz = FF(0.0f, s.twz, FF(s.twx, r.ax, FM(s.twy, r.ay)));
@@ -74,14 +86,20 @@ __device__ __forceinline__ bool intersect(const PixelRay &r, const SurfelRec &s,
   h.pz = FF(h.kx, h.ly, -FM(h.ky, h.lx));
   h.px = FF(h.ky, h.lz, -FM(h.kz, h.ly));
   h.py = FF(h.kz, h.lx, -FM(h.kx, h.lz));
-  if (h.pz == 0.0f) return false;
-  h.sx = __fdiv_rn(h.px, h.pz);
-  h.sy = __fdiv_rn(h.py, h.pz);
-  h.rho3d = FF(h.sx, h.sx, FM(h.sy, h.sy));
   h.dx = FS(s.cx, r.pxf);
   h.dy = FS(s.cy, r.pyf);
   float t = FF(h.dy, h.dy, FM(h.dx, h.dx));
   h.rho2d = FA(t, t);   // FilterInvSquare = 2
+  if (h.pz == 0.0f) return false;
+  const bool far3d = h.px * h.px + h.py * h.py > cut * (h.pz * h.pz);
+  return !(far3d && h.rho2d > cut);
+}
+
+// Second half (forward.cu:273-301).  Returns false when the reference would `continue`.
+__device__ __forceinline__ bool intersect_finish(const PixelRay &r, const SurfelRec &s, Hit &h) {
+  h.sx = __fdiv_rn(h.px, h.pz);
+  h.sy = __fdiv_rn(h.py, h.pz);
+  h.rho3d = FF(h.sx, h.sx, FM(h.sy, h.sy));
   h.bx = FA(s.twx, FF(s.tux, h.sx, FM(s.tvx, h.sy)));
   h.by = FA(s.twy, FF(s.tuy, h.sx, FM(s.tvy, h.sy)));
   h.bz = FA(s.twz, FF(s.tuz, h.sx, FM(s.tvz, h.sy)));
@@ -101,6 +119,26 @@ __device__ __forceinline__ bool intersect(const PixelRay &r, const SurfelRec &s,
   return true;
 }
 
+// Branch-free form of intersect_finish (same floats, same verdict): lets the compiler
+// interleave two evaluations.  h must come from intersect_begin; lanes for which that
+// returned false may compute garbage here, the caller masks them.
+__device__ __forceinline__ bool intersect_finish_nb(const PixelRay &r, const SurfelRec &s, Hit &h) {
+  h.sx = __fdiv_rn(h.px, h.pz);
+  h.sy = __fdiv_rn(h.py, h.pz);
+  h.rho3d = FF(h.sx, h.sx, FM(h.sy, h.sy));
+  h.bx = FA(s.twx, FF(s.tux, h.sx, FM(s.tvx, h.sy)));
+  h.by = FA(s.twy, FF(s.tuy, h.sx, FM(s.tvy, h.sy)));
+  h.bz = FA(s.twz, FF(s.tuz, h.sx, FM(s.tvz, h.sy)));
+  const float valid = FF(r.Z, h.bz, FF(r.X, h.bx, FM(r.Y, h.by)));
+  const float d3 = __fsqrt_rn(FF(h.bz, h.bz, FF(h.bx, h.bx, FM(h.by, h.by))));
+  h.depth = (h.rho3d <= h.rho2d) ? d3 : s.d2d;
+  const float power = FM(fminf(h.rho3d, h.rho2d), -0.5f);
+  h.G = expf(power);
+  h.alpha = fminf(0.99f, FM(s.opa, h.G));
+  return !(valid < 0.0f) && !(h.depth < SPLAT_NEAR) && !(power > 0.0f) &&
+         !(h.alpha < __uint_as_float(SPLAT_ALPHA_MIN));
+}
+
 // Does the surfel's cull box (see dssr_preprocess.cu:cull_box) touch the pixel
 // rectangle [x0,x1] x [y0,y1]?  x is periodic with the azimuth period.  Written so
 // that any NaN answers "yes".
@@ -108,4 +146,22 @@ __device__ __forceinline__ bool cull_overlap(float4 cb, float x0, float x1, floa
                                              float y1, float inv_period) {
   return !(cb.z > y1) && !(cb.w < y0) &&
          !(floorf((x1 - cb.x) * inv_period) < ceilf((x0 - cb.y) * inv_period));
+}
+
+// Which of the 16 4x4-pixel sub-tiles of the 16x16 tile at (tx0, ty0) can the surfel's cull
+// box touch?  bit (sy*4 + sx).  Same NaN-means-yes convention as cull_overlap.
+__device__ __forceinline__ uint32_t subtile_mask(float4 cb, float tx0, float ty0,
+                                                 float inv_period) {
+  uint32_t rm = 0, cm = 0;
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const float y0 = ty0 + 4.0f * i, x0 = tx0 + 4.0f * i;
+    if (!(cb.z > y0 + 3.0f) && !(cb.w < y0)) rm |= 1u << i;
+    if (!(floorf((x0 + 3.0f - cb.x) * inv_period) < ceilf((x0 - cb.y) * inv_period))) cm |= 1u << i;
+  }
+  uint32_t m = 0;
+#pragma unroll
+  for (int r = 0; r < 4; r++)
+    if (rm & (1u << r)) m |= cm << (4 * r);
+  return m;
 }
