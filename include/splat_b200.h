@@ -95,6 +95,13 @@ typedef struct {
   float *dL_dtransMat;           /* [P,12]                                         */
   float *dL_dscales;             /* [P,2]                                          */
   float *dL_drotations;          /* [P,4]                                          */
+  /* Optional (NULL = off; no counterpart in the reference): a contiguous [P,10] buffer
+   * (dL_dmeans3D 3 | dL_dopacity 1 | dL_dscales 2 | dL_drotations 4 per surfel, 8-byte
+   * aligned) that receives the same gradients, overwritten or - with packed_accumulate -
+   * added to.  It is the message of the keyframe-window all-reduce: a rank accumulates
+   * all of its keyframes into it without any extra kernel. */
+  float *packed_grads;
+  int packed_accumulate;
   void *stream;
 } dssr_backward_args;
 

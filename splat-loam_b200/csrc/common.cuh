@@ -296,6 +296,8 @@ struct BwdParams {
   const float *dL_dout;
   float *dL_dmeans2D, *dL_dnormal, *dL_dopacity, *dL_dmeans3D, *dL_dtransMat,
       *dL_dscales, *dL_drotations;
+  float *packed;          // optional [P,10]
+  int packed_accumulate;
 };
 void launch_render_backward(const BwdParams &p, const GeomView &g, const ImageView &im,
                             const BinView &b, cudaStream_t s);

@@ -133,7 +133,7 @@ int splat_fail(const char *fmt, ...) {
 extern "C" {
 
 const char *splat_last_error(void) { return g_err.c_str(); }
-int splat_abi_version(void) { return 1; }
+int splat_abi_version(void) { return 2; }
 
 size_t dssr_geometry_bytes(int P) { return GeomLayout(P < 0 ? 0 : P).total; }
 size_t dssr_image_bytes(int W, int H) { return ImageLayout(W, H).total; }
@@ -261,7 +261,7 @@ int dssr_backward(const dssr_backward_args *a) {
     return fail("dssr_backward: NULL input pointer");
   if (((uintptr_t)a->scales & 7) || ((uintptr_t)a->rotations & 15) ||
       ((uintptr_t)a->dL_dscales & 7) || ((uintptr_t)a->dL_drotations & 15) ||
-      ((uintptr_t)a->dL_dtransMat & 15))
+      ((uintptr_t)a->dL_dtransMat & 15) || ((uintptr_t)a->packed_grads & 7))
     return fail("dssr_backward: scales / dL_dscales must be 8-byte and rotations / "
                 "dL_drotations / dL_dtransMat 16-byte aligned");
   const bool dbg = a->debug & 1;
@@ -283,6 +283,8 @@ int dssr_backward(const dssr_backward_args *a) {
   bp.dL_dopacity = a->dL_dopacity; bp.dL_dmeans3D = a->dL_dmeans3D;
   bp.dL_dtransMat = a->dL_dtransMat; bp.dL_dscales = a->dL_dscales;
   bp.dL_drotations = a->dL_drotations;
+  bp.packed = a->packed_grads;
+  bp.packed_accumulate = a->packed_accumulate;
   {
     ProfScope ps("render_backward", st);
     launch_render_backward(bp, gv, iv, bv, st);

@@ -320,8 +320,10 @@ backward_preprocess_kernel(int P, const int *__restrict__ radii,
                            const float *__restrict__ rotations,
                            const float *__restrict__ viewmatrix,
                            const float *__restrict__ dL_dtransMat,
-                           const float *__restrict__ dL_dnormal, float *dL_dmeans3D,
-                           float *dL_dscales, float *dL_drot) {
+                           const float *__restrict__ dL_dnormal,
+                           const float *__restrict__ dL_dopacity, float *dL_dmeans3D,
+                           float *dL_dscales, float *dL_drot, float *packed,
+                           int packed_accumulate) {
   __shared__ float m[16];
   if (threadIdx.x < 16) m[threadIdx.x] = viewmatrix[threadIdx.x];
   __syncthreads();
@@ -386,6 +388,17 @@ backward_preprocess_kernel(int P, const int *__restrict__ radii,
   dL_dmeans3D[3 * (size_t)idx + 2] = dmean.z;
   reinterpret_cast<float2 *>(dL_dscales)[idx] = dscale;
   reinterpret_cast<float4 *>(dL_drot)[idx] = dq;
+  if (packed) {   // [means3D 3 | opacity 1 | scales 2 | rotations 4]
+    float2 *row = reinterpret_cast<float2 *>(packed + 10 * (size_t)idx);
+    float2 r0 = make_float2(dmean.x, dmean.y), r1 = make_float2(dmean.z, dL_dopacity[idx]),
+           r2 = dscale, r3 = make_float2(dq.x, dq.y), r4 = make_float2(dq.z, dq.w);
+    if (packed_accumulate) {
+      const float2 o0 = row[0], o1 = row[1], o2 = row[2], o3 = row[3], o4 = row[4];
+      r0.x += o0.x; r0.y += o0.y; r1.x += o1.x; r1.y += o1.y; r2.x += o2.x; r2.y += o2.y;
+      r3.x += o3.x; r3.y += o3.y; r4.x += o4.x; r4.y += o4.y;
+    }
+    row[0] = r0; row[1] = r1; row[2] = r2; row[3] = r3; row[4] = r4;
+  }
 }
 
 }  // namespace
@@ -401,5 +414,6 @@ void launch_render_backward(const BwdParams &p, const GeomView &g, const ImageVi
 void launch_backward_preprocess(const BwdParams &p, cudaStream_t s) {
   backward_preprocess_kernel<<<(p.P + 255) / 256, 256, 0, s>>>(
       p.P, p.radii, p.scales, p.rotations, p.viewmatrix, p.dL_dtransMat, p.dL_dnormal,
-      p.dL_dmeans3D, p.dL_dscales, p.dL_drotations);
+      p.dL_dopacity, p.dL_dmeans3D, p.dL_dscales, p.dL_drotations, p.packed,
+      p.packed_accumulate);
 }

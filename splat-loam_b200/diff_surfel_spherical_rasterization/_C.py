@@ -101,7 +101,12 @@ def rasterize_gaussians(means3D, opacity, scales, rotations, scale_modifier, tra
 
 def rasterize_gaussians_backward(means3D, radii, scales, rotations, scale_modifier,
                                  transMat_precomp, viewmatrix, projmatrix, dL_dout, geomBuffer,
-                                 R, binningBuffer, imageBuffer, debug):
+                                 R, binningBuffer, imageBuffer, debug, packed=None,
+                                 packed_accumulate=False):
+    """Reference signature (rasterize_points.cu:90-147).  Extension: `packed`, a contiguous
+    float32 [P,10] tensor that additionally receives (or, with packed_accumulate, is
+    incremented by) dL_dmeans3D | dL_dopacity | dL_dscales | dL_drotations - the message of
+    the keyframe-window all-reduce."""
     for t, nm in ((means3D, "means3D"), (radii, "radii"), (scales, "scales"),
                   (rotations, "rotations"), (transMat_precomp, "transMat_precomp"),
                   (viewmatrix, "viewmatrix"), (projmatrix, "projmatrix"),
@@ -111,6 +116,9 @@ def rasterize_gaussians_backward(means3D, radii, scales, rotations, scale_modifi
     P = int(means3D.size(0))
     H, W = int(dL_dout.size(1)), int(dL_dout.size(2))
     dev = means3D.device
+    if packed is not None and (packed.dtype != torch.float32 or not packed.is_contiguous()
+                               or tuple(packed.shape) != (P, 10) or packed.device != dev):
+        raise RuntimeError("packed must be a contiguous float32 CUDA tensor of shape [P,10]")
     with torch.cuda.device(dev):
         # one allocation, seven contiguous slices (the reference does seven torch::zeros,
         # rasterize_points.cu:116-122; the kernels here write every element themselves)
@@ -133,7 +141,9 @@ def rasterize_gaussians_backward(means3D, radii, scales, rotations, scale_modifi
                 _ptr(view_c), _ptr(proj_c), _ptr(radii_c),
                 _ptr(geomBuffer), _ptr(binningBuffer), _ptr(imageBuffer), _ptr(dout_c),
                 _ptr(dmeans2D), _ptr(dnormal), _ptr(dopacity), _ptr(dmeans3D), _ptr(dtrans),
-                _ptr(dscales), _ptr(drot), torch.cuda.current_stream(dev).cuda_stream)
+                _ptr(dscales), _ptr(drot),
+                _ptr(packed) if packed is not None else None, int(bool(packed_accumulate)),
+                torch.cuda.current_stream(dev).cuda_stream)
             _n.check(_lib.dssr_backward(ctypes.byref(a)))
     return dmeans2D, dopacity, dmeans3D, dtrans, dscales, drot
 

@@ -21,10 +21,11 @@ def shard_keyframes(num_keyframes, rank, world_size):
     return list(range(rank, num_keyframes, world_size))
 
 
-def cuda_frame_grads(params, camera, dL_dout_fn):
+def cuda_frame_grads(params, camera, dL_dout_fn, out=None):
     """One keyframe through the CUDA rasterizer (drop-in `_C`): returns [P,10] gradients and
     the rendered map.  `camera` = (viewmatrix, projmatrix, H, W); `dL_dout_fn(allmap)` gives the
-    upstream gradient of the 7xHxW map."""
+    upstream gradient of the 7xHxW map.  With `out` ([P,10]) the per-surfel VJP kernel adds
+    its result straight into that buffer (no concatenation or add kernels)."""
     from diff_surfel_spherical_rasterization import _C
     means3D, opacities, scales, rotations = params
     view, proj, H, W = camera
@@ -32,9 +33,12 @@ def cuda_frame_grads(params, camera, dL_dout_fn):
     R, allmap, radii, geom, binning, img = _C.rasterize_gaussians(
         means3D, opacities, scales, rotations, 1.0, empty, view, proj, H, W, False, False)
     dL = dL_dout_fn(allmap)
-    _, d_opa, d_means, _, d_scales, d_rots = _C.rasterize_gaussians_backward(
-        means3D, radii, scales, rotations, 1.0, empty, view, proj, dL, geom, R, binning, img, False)
-    return torch.cat([d_means, d_opa, d_scales, d_rots], dim=1), allmap
+    packed = out if out is not None else torch.empty((means3D.shape[0], GRAD_COLS),
+                                                     dtype=torch.float32, device=means3D.device)
+    _C.rasterize_gaussians_backward(means3D, radii, scales, rotations, 1.0, empty, view, proj, dL,
+                                    geom, R, binning, img, False, packed=packed,
+                                    packed_accumulate=out is not None)
+    return packed, allmap
 
 
 class KeyframeWindow:
@@ -59,8 +63,11 @@ class KeyframeWindow:
         buf = self._buf.zero_()
         mine = shard_keyframes(len(cameras), rank, world)
         for k in mine:
-            g, _ = self.frame_fn(params, cameras[k], lambda m, k=k: dL_dout_fn(k, m))
-            buf += g
+            if self.frame_fn is cuda_frame_grads:   # accumulates in place
+                self.frame_fn(params, cameras[k], lambda m, k=k: dL_dout_fn(k, m), out=buf)
+            else:
+                g, _ = self.frame_fn(params, cameras[k], lambda m, k=k: dL_dout_fn(k, m))
+                buf += g
         return buf, mine
 
     def gradients(self, params, cameras, dL_dout_fn):

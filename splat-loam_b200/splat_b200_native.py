@@ -44,6 +44,7 @@ class DssrBackwardArgs(ctypes.Structure):
         ("dL_dmeans2D", c_float_p), ("dL_dnormal", c_float_p), ("dL_dopacity", c_float_p),
         ("dL_dmeans3D", c_float_p), ("dL_dtransMat", c_float_p), ("dL_dscales", c_float_p),
         ("dL_drotations", c_float_p),
+        ("packed_grads", c_float_p), ("packed_accumulate", ctypes.c_int),
         ("stream", ctypes.c_void_p),
     ]
 

@@ -42,6 +42,14 @@ def viewmatrix(k=0):
     return np.ascontiguousarray(np.linalg.inv(pose(k)).T, dtype=np.float32)
 
 
+def yaw_viewmatrix(deg):
+    """View matrix of a sensor at the origin rotated by `deg` about its vertical axis."""
+    a = math.radians(deg)
+    T = np.eye(4)
+    T[:3, :3] = [[math.cos(a), -math.sin(a), 0], [math.sin(a), math.cos(a), 0], [0, 0, 1]]
+    return np.ascontiguousarray(np.linalg.inv(T).T, dtype=np.float32)
+
+
 def _rotmat_to_quat(R):
     """(w,x,y,z) of a batch of rotation matrices [n,3,3] (Shepperd's method)."""
     n = R.shape[0]

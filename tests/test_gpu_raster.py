@@ -253,3 +253,43 @@ def test_empty_and_degenerate_inputs():
     b = _C.rasterize_gaussians(c["means3D"], c["opacities"], c["scales"], c["rotations"], 1.0, e,
                                c["viewmatrix"], c["projmatrix"], s["H"], s["W"], False, False)
     assert a[0] == b[0] and torch.equal(a[1], b[1])
+
+
+def test_packed_gradients_and_keyframe_window():
+    """The [P,10] packed output of the per-surfel VJP equals the separate gradient tensors,
+    accumulates in place, and a (single-rank) keyframe window equals the sum over its
+    keyframes of single-frame gradients (SURVEY.md §8e parity)."""
+    from diff_surfel_spherical_rasterization import _C
+    from keyframe_window import KeyframeWindow
+    s = scenes.make_scene("C0")
+    c = to_cuda(s)
+    e = torch.empty(0, device="cuda")
+    P = s["means3D"].shape[0]
+    params = (c["means3D"], c["opacities"], c["scales"], c["rotations"])
+    cams = [(torch.from_numpy(scenes.viewmatrix(k)).cuda(), c["projmatrix"], s["H"], s["W"])
+            for k in range(3)]
+    singles = []
+    for view, proj, H, W in cams:
+        R, out, radii, geom, binning, img = _C.rasterize_gaussians(
+            *params, 1.0, e, view, proj, H, W, False, False) if False else _C.rasterize_gaussians(
+            c["means3D"], c["opacities"], c["scales"], c["rotations"], 1.0, e, view, proj, H, W,
+            False, False)
+        packed = torch.full((P, 10), 7.0, device="cuda")
+        g = _C.rasterize_gaussians_backward(c["means3D"], radii, c["scales"], c["rotations"], 1.0, e,
+                                            view, proj, c["dL_dout"], geom, R, binning, img, False,
+                                            packed=packed)
+        cat = torch.cat([g[2], g[1], g[4], g[5]], dim=1)
+        assert torch.equal(packed, cat)                       # overwritten, bit-identical
+        _C.rasterize_gaussians_backward(c["means3D"], radii, c["scales"], c["rotations"], 1.0, e,
+                                        view, proj, c["dL_dout"], geom, R, binning, img, False,
+                                        packed=packed, packed_accumulate=True)
+        assert rel_l2(packed.cpu().numpy(), 2.0 * cat.cpu().numpy().astype(np.float64)) < 1e-6
+        singles.append(cat.double())
+    total = KeyframeWindow().gradients(params, cams, lambda k, m: c["dL_dout"])
+    want = sum(singles)
+    assert rel_l2(total.cpu().numpy(), want.cpu().numpy()) < 1e-5
+    assert cosine(total.cpu().numpy(), want.cpu().numpy()) > 0.999999
+    with pytest.raises(RuntimeError, match="packed"):
+        _C.rasterize_gaussians_backward(c["means3D"], radii, c["scales"], c["rotations"], 1.0, e,
+                                        view, proj, c["dL_dout"], geom, R, binning, img, False,
+                                        packed=torch.zeros(P, 9, device="cuda"))
