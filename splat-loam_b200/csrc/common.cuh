@@ -270,7 +270,8 @@ void launch_emit(const FwdParams &p, const GeomView &g, const ImageView &im,
 void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, const BinView &b,
                  const SortPlan &sp, uint32_t capacity, cudaStream_t s);
 void launch_digit_scan(const uint32_t *hist, uint32_t *digit_base, int npass, uint2 *ranges,
-                       int tiles, int tile_pass_single, int nrepl, cudaStream_t s);
+                       uint32_t *tile_order, int tiles, int tile_pass_single, int nrepl,
+                       cudaStream_t s);
 struct MaskParams {          // what the last sort pass needs to emit sub_mask (may be all 0)
   uint16_t *sub_mask;
   const float4 *cull;
@@ -279,7 +280,6 @@ struct MaskParams {          // what the last sort pass needs to emit sub_mask (
 };
 unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long *b,
                                        unsigned long long *keys_out, uint32_t *plist_out,
-                                       MaskParams mp,
                                        const uint32_t *num_ptr, uint32_t capacity,
                                        uint32_t *status, const size_t *status_off,
                                        uint32_t *tickets, const uint32_t *digit_base,

@@ -41,8 +41,10 @@ __device__ __forceinline__ void st_volatile_u32(uint32_t *p, uint32_t v) {
 // reference's memset + identifyTileRanges leaves).
 __global__ void __launch_bounds__(SORT_MAX_BINS)
 digit_scan_kernel(const uint32_t *__restrict__ hist, uint32_t *__restrict__ digit_base,
-                  uint2 *ranges, int tiles, int tile_pass_single, int nrepl) {
+                  uint2 *ranges, uint32_t *tile_order, int tiles, int tile_pass_single,
+                  int nrepl) {
   __shared__ uint32_t s_warp[32];
+  __shared__ uint32_t s_len[SORT_MAX_BINS];
   const int pass = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   uint32_t v = 0;
 #pragma unroll 8
@@ -68,8 +70,19 @@ digit_scan_kernel(const uint32_t *__restrict__ hist, uint32_t *__restrict__ digi
   __syncthreads();
   uint32_t excl = s_warp[wid] + inc - v;
   digit_base[pass * SORT_MAX_BINS + tid] = excl;
-  if (pass == tile_pass_single && tid < tiles)
-    ranges[tid] = v ? make_uint2(excl, excl + v) : make_uint2(0u, 0u);
+  if (pass != tile_pass_single) return;
+  if (tid < tiles) ranges[tid] = v ? make_uint2(excl, excl + v) : make_uint2(0u, 0u);
+  // tile_order[rank] = tile, by decreasing list length (see tile_order_kernel)
+  s_len[tid] = v;
+  __syncthreads();
+  if (tid < tiles && tile_order) {
+    uint32_t rank = 0;
+    for (int o = 0; o < tiles; o++) {
+      const uint32_t l = s_len[o];
+      rank += (l > v) || (l == v && o < tid);
+    }
+    tile_order[rank] = (uint32_t)tid;
+  }
 }
 
 // identifyTileRanges (rasterizer_impl.cu:94-114) for the > 1024 tiles case.
@@ -89,6 +102,29 @@ __global__ void identify_ranges_kernel(const uint32_t *num_ptr, uint32_t capacit
     }
   }
   if (i == L - 1) ranges[cur].y = L;
+}
+
+// sub_mask[i]: which 4x4 sub-tiles of its tile the i-th sorted instance's cull box can touch
+// (consumed by the compositing kernels instead of re-testing boxes in their inner loops).
+__global__ void __launch_bounds__(256)
+sub_mask_kernel(const uint32_t *__restrict__ num_ptr, uint32_t capacity,
+                const unsigned long long *__restrict__ keys,
+                const uint32_t *__restrict__ point_list, MaskParams mp, uint32_t P) {
+  const uint32_t N = min(*num_ptr, capacity);
+  const uint32_t i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= N) return;
+  const float fx = mp.projmatrix[0], fy = mp.projmatrix[5], cy = mp.projmatrix[9];
+  const float inv_period = 1.0f / (6.2831853f * fabsf(fx));
+  // culling assumes |elevation| < pi/2 on every image row
+  const bool cull_on = fmaxf(fabsf((0.0f - cy) / fy), fabsf(((float)(mp.H - 1) - cy) / fy)) < 1.55f;
+  uint32_t sm = 0xffffu;
+  if (cull_on) {
+    const uint32_t t = (uint32_t)(keys[i] >> 32);
+    const uint32_t id = min(point_list[i], P - 1u);
+    sm = subtile_mask(mp.cull[id], (float)((t % mp.tiles_x) * SPLAT_TILE),
+                      (float)((t / mp.tiles_x) * SPLAT_TILE), inv_period);
+  }
+  mp.sub_mask[i] = (uint16_t)sm;
 }
 
 // tile_order[rank] = tile, rank by decreasing list length (ties by index): the compositing
@@ -112,12 +148,13 @@ __global__ void tile_order_kernel(const uint2 *__restrict__ ranges, int tiles,
 // have already started), ranks its 4096 words stably per digit with warp match-any,
 // publishes its digit counts, resolves its global offsets by looking back over the
 // predecessors' published counts, and scatters.
+template <bool LAST>
 __global__ void __launch_bounds__(SORT_THREADS)
 sort_pass_kernel(const unsigned long long *__restrict__ in, unsigned long long *out,
-                 unsigned long long *keys_out, uint32_t *plist_out, MaskParams mp,
+                 unsigned long long *keys_out, uint32_t *plist_out,
                  const uint32_t *__restrict__ num_ptr, uint32_t capacity, uint32_t *status,
                  uint32_t *ticket, const uint32_t *__restrict__ digit_base, int shift,
-                 int bits, int last, int idx_bits) {
+                 int bits, int idx_bits) {
   extern __shared__ uint32_t smem[];
   const int bins = 1 << bits;
   uint16_t *s_cnt = reinterpret_cast<uint16_t *>(smem);            // [WARPS][bins]
@@ -195,14 +232,6 @@ sort_pass_kernel(const unsigned long long *__restrict__ in, unsigned long long *
   __syncthreads();
 
   const unsigned long long idx_mask = (1ull << idx_bits) - 1ull;
-  float inv_period = 0.0f;
-  bool cull_on = false;
-  if (last && mp.sub_mask) {
-    const float fx = mp.projmatrix[0], fy = mp.projmatrix[5], cy = mp.projmatrix[9];
-    inv_period = 1.0f / (6.2831853f * fabsf(fx));
-    // culling assumes |elevation| < pi/2 on every image row
-    cull_on = fmaxf(fabsf((0.0f - cy) / fy), fabsf(((float)(mp.H - 1) - cy) / fy)) < 1.55f;
-  }
 #pragma unroll
   for (int r = 0; r < SORT_ITEMS; r++) {
     uint32_t i = wstart + r * 32 + lane;
@@ -210,22 +239,13 @@ sort_pass_kernel(const unsigned long long *__restrict__ in, unsigned long long *
       uint32_t digit = (uint32_t)(key[r] >> shift) & mask;
       uint32_t pos = s_base[digit] + my_cnt[digit] + rank[r];
       if (pos >= capacity) continue;  // only when the capacity hint was too small
-      if (last) {
+      if (LAST) {
         unsigned long long k = key[r];
         uint32_t idx = (uint32_t)(k & idx_mask);
         uint32_t d27 = (uint32_t)(k >> idx_bits) & ((1u << SPLAT_DEPTH_BITS) - 1u);
         unsigned long long tile = k >> (idx_bits + SPLAT_DEPTH_BITS);
         keys_out[pos] = (tile << 32) | (unsigned long long)(d27 + SPLAT_DEPTH_BASE);
         plist_out[pos] = idx;
-        if (mp.sub_mask) {
-          uint32_t sm = 0xffffu;
-          if (cull_on) {
-            const uint32_t t = (uint32_t)tile;
-            sm = subtile_mask(mp.cull[idx], (float)((t % mp.tiles_x) * SPLAT_TILE),
-                              (float)((t / mp.tiles_x) * SPLAT_TILE), inv_period);
-          }
-          mp.sub_mask[pos] = (uint16_t)sm;
-        }
       } else {
         out[pos] = key[r];
       }
@@ -236,8 +256,9 @@ sort_pass_kernel(const unsigned long long *__restrict__ in, unsigned long long *
 }  // namespace
 
 void launch_digit_scan(const uint32_t *hist, uint32_t *digit_base, int npass, uint2 *ranges,
-                       int tiles, int tile_pass_single, int nrepl, cudaStream_t s) {
-  digit_scan_kernel<<<npass, SORT_MAX_BINS, 0, s>>>(hist, digit_base, ranges, tiles,
+                       uint32_t *tile_order, int tiles, int tile_pass_single, int nrepl,
+                       cudaStream_t s) {
+  digit_scan_kernel<<<npass, SORT_MAX_BINS, 0, s>>>(hist, digit_base, ranges, tile_order, tiles,
                                                     tile_pass_single, nrepl);
 }
 
@@ -246,7 +267,6 @@ void launch_digit_scan(const uint32_t *hist, uint32_t *digit_base, int npass, ui
 // Returns the array that holds the sorted words otherwise.
 unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long *b,
                                        unsigned long long *keys_out, uint32_t *plist_out,
-                                       MaskParams mp,
                                        const uint32_t *num_ptr, uint32_t capacity,
                                        uint32_t *status, const size_t *status_off,
                                        uint32_t *tickets, const uint32_t *digit_base,
@@ -257,10 +277,14 @@ unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long
   for (int p = 0; p < npass; p++) {
     const int nbins = 1 << bits[p];
     const size_t smem = (size_t)WARPS * nbins * 2 + (size_t)nbins * 4;
-    const int last = unpack_last && (p == npass - 1);
-    sort_pass_kernel<<<nblk, SORT_THREADS, smem, s>>>(
-        src, dst, keys_out, plist_out, mp, num_ptr, capacity, status + status_off[p],
-        tickets + p, digit_base + p * SORT_MAX_BINS, shift[p], bits[p], last, idx_bits);
+    if (unpack_last && p == npass - 1)
+      sort_pass_kernel<true><<<nblk, SORT_THREADS, smem, s>>>(
+          src, dst, keys_out, plist_out, num_ptr, capacity, status + status_off[p], tickets + p,
+          digit_base + p * SORT_MAX_BINS, shift[p], bits[p], idx_bits);
+    else
+      sort_pass_kernel<false><<<nblk, SORT_THREADS, smem, s>>>(
+          src, dst, keys_out, plist_out, num_ptr, capacity, status + status_off[p], tickets + p,
+          digit_base + p * SORT_MAX_BINS, shift[p], bits[p], idx_bits);
     unsigned long long *t = dst;
     dst = src;
     src = t;
@@ -277,8 +301,9 @@ void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, con
   mp.tiles_x = im.tiles_x;
   mp.H = p.H;
   const int single = (sp.npass == 4) ? 3 : -1;
-  launch_digit_scan(b.hist, b.digit_base, sp.npass, im.ranges, im.tiles, single, HIST_REPL, s);
-  launch_sort_passes(b.words_a, b.words_b, b.keys, b.point_list, mp, &g.hdr->num_rendered,
+  launch_digit_scan(b.hist, b.digit_base, sp.npass, im.ranges, im.tile_order, im.tiles, single,
+                    HIST_REPL, s);
+  launch_sort_passes(b.words_a, b.words_b, b.keys, b.point_list, &g.hdr->num_rendered,
                      capacity, b.status, b.status_off, b.tickets, b.digit_base, sp.npass,
                      sp.shift, sp.bits, 1, sp.idx_bits, b.nblk, s);
   if (single < 0) {
@@ -288,5 +313,9 @@ void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, con
       identify_ranges_kernel<<<blocks, 256, 0, s>>>(&g.hdr->num_rendered, capacity, b.keys,
                                                     im.ranges);
   }
-  tile_order_kernel<<<(im.tiles + 127) / 128, 128, 0, s>>>(im.ranges, im.tiles, im.tile_order);
+  if (single < 0)
+    tile_order_kernel<<<(im.tiles + 127) / 128, 128, 0, s>>>(im.ranges, im.tiles, im.tile_order);
+  if (capacity)
+    sub_mask_kernel<<<(capacity + 255) / 256, 256, 0, s>>>(&g.hdr->num_rendered, capacity, b.keys,
+                                                           b.point_list, mp, (uint32_t)p.P);
 }

@@ -281,9 +281,9 @@ int sknn_dist2(int P, const float *points, float *mean_dists, void *workspace,
   bbox_partial_kernel<<<bb, 256, 0, st>>>(P, points, partial);
   bbox_final_kernel<<<1, 32, 0, st>>>(bb, partial, num, P);
   morton_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, points, partial + BB_BLOCKS * 6, wa, hist);
-  launch_digit_scan(hist, digit_base, 3, nullptr, 0, -1, 1, st);
+  launch_digit_scan(hist, digit_base, 3, nullptr, nullptr, 0, -1, 1, st);
   const int shift[3] = {32, 42, 52}, bits[3] = {10, 10, 10};
-  unsigned long long *res = launch_sort_passes(wa, wb, nullptr, nullptr, MaskParams{}, num, (uint32_t)P, status,
+  unsigned long long *res = launch_sort_passes(wa, wb, nullptr, nullptr, num, (uint32_t)P, status,
                                                L.status_off, tickets, digit_base, 3, shift, bits,
                                                0, 32, L.nblk, st);
   const int leaves = (P + LEAF - 1) / LEAF;
