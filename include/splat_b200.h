@@ -148,7 +148,7 @@ SPLAT_API int sknn_dist2(int P, const float *points, float *mean_dists, void *wo
  * (cudaMalloc / cudaFree serialise the device), a process whose GPU memory already belongs
  * to another framework's caching allocator, a plug-in that may not make allocating CUDA
  * calls.  Inputs and output as sknn_dist2; the scratch is a file-scope device array inside
- * the library (about 3 MB on every GPU that loads it, held until exit), so:
+ * the library (4 MB on every GPU that loads it, held until exit), so:
  *   - P must not exceed SKNN_STATIC_MAX_POINTS, larger clouds are refused with an error;
  *   - the first call on a device resolves the array's address on that device; make it
  *     before any stream capture begins;

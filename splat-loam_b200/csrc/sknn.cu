@@ -9,10 +9,12 @@
 // 1024 distance evaluations per surviving box).  Its pruning is conservative, so what
 // it returns is the exact 3-NN; any exact 3-NN search that evaluates a distance as
 //   d = p - q;  dist = fma(d.z, d.z, fma(d.x, d.x, d.y*d.y))      (the compiled form)
-// and keeps the three smallest returns the same floats.  Here: same Morton order (our
-// own radix sort), but an implicit 8-ary box hierarchy over 32-point leaves that each
-// point descends with a small stack, so the work per point is O(log P) box tests and
-// a handful of leaves, and no cudaMalloc / host round trip happens inside the call.
+// and keeps the three smallest returns the same floats.  Here: a Morton order too (our own
+// radix sort), but at up to 20 bits per axis instead of 10 (the reference's 10-bit cells
+// are ~25 cm on an accumulated LiDAR cloud, hundreds of points each), and an implicit
+// 8-ary box hierarchy over 32-point leaves that each point descends with a small stack, so
+// the work per point is O(log P) box tests and a handful of leaves, and no cudaMalloc /
+// host round trip happens inside the call.
 #include <cfloat>
 
 #include "../../include/splat_b200.h"
@@ -24,6 +26,28 @@ constexpr int LEAF = 32;
 constexpr int FAN = 8;
 constexpr int MAXL = 12;
 constexpr int BB_BLOCKS = 256;
+
+// Morton code width: as many bits per axis as fit a 64-bit [code | index] word, at most 20.
+struct KnnPlan {
+  int idx_bits, axis_bits, npass;
+  int shift[SORT_MAX_PASSES], bits[SORT_MAX_PASSES];
+  __host__ explicit KnnPlan(int P) {
+    idx_bits = 1;
+    while ((1ll << idx_bits) < (long long)P) idx_bits++;
+    axis_bits = (64 - idx_bits) / 3;
+    if (axis_bits > 20) axis_bits = 20;
+    const int total = 3 * axis_bits;
+    npass = (total + 9) / 10;
+    int sh = idx_bits, left = total;
+    for (int i = 0; i < npass; i++) {
+      const int b = (left + (npass - i) - 1) / (npass - i);
+      shift[i] = sh;
+      bits[i] = b;
+      sh += b;
+      left -= b;
+    }
+  }
+};
 
 struct KnnLayout {
   size_t hdr, partial, words_a, words_b, sorted, boxes, hist, tickets, status, digit_base,
@@ -54,14 +78,13 @@ struct KnnLayout {
     words_b = o;  o = align_up(o + (size_t)P * 8, 256);
     sorted = o;   o = align_up(o + (size_t)P * 16, 256);
     boxes = o;    o = align_up(o + nodes * 32, 256);
-    hist = o;     o = align_up(o + (size_t)3 * SORT_MAX_BINS * 4, 256);
+    hist = o;     o = align_up(o + (size_t)HIST_REPL * SORT_MAX_PASSES * SORT_MAX_BINS * 4, 256);
     tickets = o;  o = align_up(o + 64, 256);
     status = o;
-    for (int p = 0; p < SORT_MAX_PASSES; p++)
-      status_off[p] = (size_t)(p < 3 ? p : 0) * nblk * SORT_MAX_BINS;
-    o = align_up(o + (size_t)3 * nblk * SORT_MAX_BINS * 4, 256);
+    for (int p = 0; p < SORT_MAX_PASSES; p++) status_off[p] = (size_t)p * nblk * SORT_MAX_BINS;
+    o = align_up(o + (size_t)SORT_MAX_PASSES * nblk * SORT_MAX_BINS * 4, 256);
     zero_bytes = o - hist;
-    digit_base = o; o = align_up(o + (size_t)3 * SORT_MAX_BINS * 4, 256);
+    digit_base = o; o = align_up(o + (size_t)SORT_MAX_PASSES * SORT_MAX_BINS * 4, 256);
     total = o + 256;
   }
 };
@@ -117,51 +140,71 @@ bbox_partial_kernel(int P, const float *__restrict__ pts, float *partial) {
 __global__ void bbox_final_kernel(int nblocks, float *partial, uint32_t *num, int P) {
   const int c = threadIdx.x;
   if (c < 6) {
-    float r = 0.0f;  // the reduction's init value: the origin is part of the box
-    for (int b = 0; b < nblocks; b++)
+    // (the reference's reduction starts from the origin; the order we sort in is ours to
+    // choose, the result does not depend on it, and a tight box gives finer cells)
+    float r = partial[c];
+    for (int b = 1; b < nblocks; b++)
       r = c < 3 ? fminf(r, partial[b * 6 + c]) : fmaxf(r, partial[b * 6 + c]);
     partial[BB_BLOCKS * 6 + c] = r;
   }
   if (c == 6) *num = (uint32_t)P;
 }
 
-// prepMorton / coord2Morton (simple_knn.cu:46-62)
-__device__ __forceinline__ uint32_t prep_morton(uint32_t x) {
-  x = (x | (x << 16)) & 0x030000FF;
-  x = (x | (x << 8)) & 0x0300F00F;
-  x = (x | (x << 4)) & 0x030C30C3;
-  x = (x | (x << 2)) & 0x09249249;
+// Morton code in the manner of coord2Morton (simple_knn.cu:46-62), `axis_bits` per axis.
+__device__ __forceinline__ unsigned long long split3(uint32_t a) {
+  unsigned long long x = a & 0x1fffffu;
+  x = (x | x << 32) & 0x1f00000000ffffull;
+  x = (x | x << 16) & 0x1f0000ff0000ffull;
+  x = (x | x << 8) & 0x100f00f00f00f00full;
+  x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+  x = (x | x << 2) & 0x1249249249249249ull;
   return x;
 }
 
+struct MortonParams {
+  int idx_bits, axis_bits, npass;
+  int shift[SORT_MAX_PASSES], bits[SORT_MAX_PASSES];
+};
+
 __global__ void __launch_bounds__(256)
 morton_kernel(int P, const float *__restrict__ pts, const float *__restrict__ bbox,
-              unsigned long long *words, uint32_t *hist) {
-  const int i = blockIdx.x * 256 + threadIdx.x;
-  if (i >= P) return;
+              unsigned long long *words, uint32_t *hist, MortonParams mp) {
+  __shared__ uint32_t s_hist[SORT_MAX_PASSES * SORT_MAX_BINS];   // 24 KB
+  for (int i = threadIdx.x; i < mp.npass * SORT_MAX_BINS; i += 256) s_hist[i] = 0u;
+  __syncthreads();
   const float mnx = bbox[0], mny = bbox[1], mnz = bbox[2];
-  const float mxx = bbox[3], mxy = bbox[4], mxz = bbox[5];
-  const float x = pts[3 * (size_t)i], y = pts[3 * (size_t)i + 1], z = pts[3 * (size_t)i + 2];
-  uint32_t cx = prep_morton((uint32_t)(__fdiv_rn(x - mnx, mxx - mnx) * 1023.0f));
-  uint32_t cy = prep_morton((uint32_t)(__fdiv_rn(y - mny, mxy - mny) * 1023.0f));
-  uint32_t cz = prep_morton((uint32_t)(__fdiv_rn(z - mnz, mxz - mnz) * 1023.0f));
-  const uint32_t code = (cx | (cy << 1) | (cz << 2)) & 0x3fffffffu;
-  words[i] = ((unsigned long long)code << 32) | (uint32_t)i;
-  atomicAdd(&hist[0 * SORT_MAX_BINS + (code & 1023u)], 1u);
-  atomicAdd(&hist[1 * SORT_MAX_BINS + ((code >> 10) & 1023u)], 1u);
-  atomicAdd(&hist[2 * SORT_MAX_BINS + (code >> 20)], 1u);
+  const float sx = 1.0f / (bbox[3] - mnx), sy = 1.0f / (bbox[4] - mny), sz = 1.0f / (bbox[5] - mnz);
+  const float qmax = (float)((1u << mp.axis_bits) - 1u);
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < P; i += gridDim.x * 256) {
+    const float x = pts[3 * (size_t)i], y = pts[3 * (size_t)i + 1], z = pts[3 * (size_t)i + 2];
+    // fminf/fmaxf drop NaNs (a flat axis gives 0 * inf): such coordinates quantise to 0
+    const uint32_t qx = (uint32_t)fminf(fmaxf((x - mnx) * sx * qmax, 0.0f), qmax);
+    const uint32_t qy = (uint32_t)fminf(fmaxf((y - mny) * sy * qmax, 0.0f), qmax);
+    const uint32_t qz = (uint32_t)fminf(fmaxf((z - mnz) * sz * qmax, 0.0f), qmax);
+    const unsigned long long code = split3(qx) | (split3(qy) << 1) | (split3(qz) << 2);
+    const unsigned long long w = (code << mp.idx_bits) | (unsigned long long)(uint32_t)i;
+    words[i] = w;
+    for (int p = 0; p < mp.npass; p++)
+      atomicAdd(&s_hist[p * SORT_MAX_BINS + ((uint32_t)(w >> mp.shift[p]) & ((1u << mp.bits[p]) - 1u))], 1u);
+  }
+  __syncthreads();
+  uint32_t *gh = hist + (size_t)(blockIdx.x % HIST_REPL) * (SORT_MAX_PASSES * SORT_MAX_BINS);
+  for (int i = threadIdx.x; i < mp.npass * SORT_MAX_BINS; i += 256) {
+    const uint32_t v = s_hist[i];
+    if (v) atomicAdd(&gh[i], v);
+  }
 }
 
 // sorted order -> float4(x, y, z, bits(original index)) and the 32-point leaf boxes
 __global__ void __launch_bounds__(256)
 gather_leaf_kernel(int P, const float *__restrict__ pts,
-                   const unsigned long long *__restrict__ words, float4 *sorted,
+                   const unsigned long long *__restrict__ words, int idx_bits, float4 *sorted,
                    float4 *boxes) {
   const int i = blockIdx.x * 256 + threadIdx.x;  // grid covers whole leaves
   float x = 0.f, y = 0.f, z = 0.f;
   const bool have = i < P;
   if (have) {
-    const uint32_t idx = (uint32_t)words[i];
+    const uint32_t idx = (uint32_t)(words[i] & ((1ull << idx_bits) - 1ull));
     x = pts[3 * (size_t)idx];
     y = pts[3 * (size_t)idx + 1];
     z = pts[3 * (size_t)idx + 2];
@@ -280,14 +323,25 @@ int sknn_dist2(int P, const float *points, float *mean_dists, void *workspace,
   if (bb > BB_BLOCKS) bb = BB_BLOCKS;
   bbox_partial_kernel<<<bb, 256, 0, st>>>(P, points, partial);
   bbox_final_kernel<<<1, 32, 0, st>>>(bb, partial, num, P);
-  morton_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, points, partial + BB_BLOCKS * 6, wa, hist);
-  launch_digit_scan(hist, digit_base, 3, nullptr, nullptr, 0, -1, 1, st);
-  const int shift[3] = {32, 42, 52}, bits[3] = {10, 10, 10};
+  const KnnPlan plan(P);
+  MortonParams mp;
+  mp.idx_bits = plan.idx_bits;
+  mp.axis_bits = plan.axis_bits;
+  mp.npass = plan.npass;
+  for (int i = 0; i < SORT_MAX_PASSES; i++) {
+    mp.shift[i] = plan.shift[i];
+    mp.bits[i] = plan.bits[i];
+  }
+  int mg = (P + 255) / 256;
+  if (mg > 148 * 4) mg = 148 * 4;
+  morton_kernel<<<mg, 256, 0, st>>>(P, points, partial + BB_BLOCKS * 6, wa, hist, mp);
+  launch_digit_scan(hist, digit_base, plan.npass, nullptr, nullptr, 0, -1, HIST_REPL, st);
   unsigned long long *res = launch_sort_passes(wa, wb, nullptr, nullptr, num, (uint32_t)P, status,
-                                               L.status_off, tickets, digit_base, 3, shift, bits,
-                                               0, 32, L.nblk, st);
+                                               L.status_off, tickets, digit_base, plan.npass,
+                                               plan.shift, plan.bits, 0, plan.idx_bits, L.nblk, st);
   const int leaves = (P + LEAF - 1) / LEAF;
-  gather_leaf_kernel<<<(leaves * LEAF + 255) / 256, 256, 0, st>>>(P, points, res, sorted, boxes);
+  gather_leaf_kernel<<<(leaves * LEAF + 255) / 256, 256, 0, st>>>(P, points, res, plan.idx_bits,
+                                                                  sorted, boxes);
   KnnLevels lv;
   lv.nlevel = L.nlevel;
   for (int l = 0; l < L.nlevel; l++) {
@@ -333,7 +387,7 @@ int sknn_dist2(int P, const float *points, float *mean_dists, void *workspace,
 //   * no cudaMalloc, cudaFree or allocating library routine is called on any path.
 #include <mutex>
 
-#define SKNN_STATIC_BYTES (3u << 20)   // >= KnnLayout(SKNN_STATIC_MAX_POINTS).total (2.4 MB)
+#define SKNN_STATIC_BYTES (4u << 20)   // >= KnnLayout(SKNN_STATIC_MAX_POINTS).total (3.4 MB)
 
 static __device__ __align__(256) unsigned char g_sknn_static_scratch[SKNN_STATIC_BYTES];
 
