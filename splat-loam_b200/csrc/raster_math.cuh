@@ -67,7 +67,8 @@ struct Hit {
 // exp(-rho/2)) is below 1/255 with a 0.4 % margin (far above any rounding of the exact
 // evaluation).  Same formula as the cull box of the preprocess kernel.
 __device__ __forceinline__ float rho_cutoff(float opa) {
-  return 2.0f * logf(255.0f * opa) * 1.002f + 0.01f;
+  // __logf: absolute error < 2^-21, three orders of magnitude inside the margin
+  return 2.0f * __logf(255.0f * opa) * 1.002f + 0.01f;
 }
 
 // First half of the evaluation: the transformed planes, their cross product and the
