@@ -29,9 +29,9 @@
 
 #define PRE_CHUNK 256             // surfels per preprocess block (one thread each)
 
-#define SORT_THREADS 256
+#define SORT_THREADS 512
 #define SORT_ITEMS 16                                  // keys per thread per pass
-#define SORT_BLOCK_ELEMS (SORT_THREADS * SORT_ITEMS)   // 4096
+#define SORT_BLOCK_ELEMS (SORT_THREADS * SORT_ITEMS)   // 8192
 #define SORT_MAX_BINS 1024
 #define SORT_MAX_PASSES 6
 #define HIST_REPL 32              // replicas of the global digit histograms
