@@ -290,7 +290,7 @@ def run_ours(args, rank, world, local_rank):
                    "parallelism": f"keyframe-sharded x{world}"},
         "e2e": {"value": world * 1e3 / (e2e_ms / args.steps), "unit": UNIT,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-        "gpu_launches": 11 * args.steps,
+        "gpu_launches": 12 * args.steps,   # 10 forward + 2 backward kernels per frame
         "stage_ms": stage_ms,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak,
                      "peak_source": peak_src, "unit": "GB/s",

@@ -27,6 +27,8 @@
 #define SPLAT_DEPTH_BITS 27       // bits(120.0f) - bits(0.1f) < 2^27
 #define SPLAT_ALPHA_MIN 0x3B808081u   // smallest float that is >= 1/255
 
+#define SPLAT_MAX_ORDERED_TILES 8192   // the O(tiles^2) work ordering is skipped beyond this
+
 #define PRE_CHUNK 256             // surfels per preprocess block (one thread each)
 
 #define SORT_THREADS 512
@@ -263,7 +265,7 @@ struct FwdParams {
 
 void launch_preprocess(const FwdParams &p, const GeomView &g, const ImageView &im,
                        cudaStream_t s);
-void launch_chunk_scan(const GeomView &g, cudaStream_t s);
+void launch_chunk_scan(const GeomView &g, uint32_t *host_out, cudaStream_t s);
 void launch_emit(const FwdParams &p, const GeomView &g, const ImageView &im,
                  const BinView &b, const SortPlan &sp, uint32_t capacity,
                  cudaStream_t s);

@@ -16,7 +16,8 @@ static thread_local std::string g_err;
 
 namespace {
 
-thread_local uint32_t *g_pinned = nullptr;      // 2 words: num_rendered, status
+thread_local uint32_t *g_pinned = nullptr;      // 2 words: num_rendered, status (mapped)
+thread_local uint32_t *g_pinned_dev = nullptr;  // the device's view of g_pinned
 thread_local cudaEvent_t g_event = nullptr;
 
 #define fail splat_fail
@@ -85,7 +86,10 @@ struct ProfScope {
 };
 
 int ensure_host_scratch() {
-  if (!g_pinned) CUDA_TRY(cudaHostAlloc((void **)&g_pinned, 64, cudaHostAllocPortable));
+  if (!g_pinned) {
+    CUDA_TRY(cudaHostAlloc((void **)&g_pinned, 64, cudaHostAllocPortable | cudaHostAllocMapped));
+    CUDA_TRY(cudaHostGetDevicePointer((void **)&g_pinned_dev, g_pinned, 0));
+  }
   if (!g_event) CUDA_TRY(cudaEventCreateWithFlags(&g_event, cudaEventDisableTiming));
   return 0;
 }
@@ -220,10 +224,9 @@ int dssr_forward(const dssr_forward_args *a, int *num_rendered) {
   {
     ProfScope ps("preprocess", st);
     launch_preprocess(fp, gv, iv, st);
-    launch_chunk_scan(gv, st);
+    launch_chunk_scan(gv, g_pinned_dev, st);   // count + status land in g_pinned
   }
   LAUNCH_CHECK(dbg, st, "preprocess");
-  CUDA_TRY(cudaMemcpyAsync(g_pinned, &gv.hdr->num_rendered, 8, cudaMemcpyDeviceToHost, st));
   CUDA_TRY(cudaEventRecord(g_event, st));
   tr.lap("enqueue preprocess");
 

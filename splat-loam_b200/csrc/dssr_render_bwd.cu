@@ -405,9 +405,9 @@ backward_preprocess_kernel(int P, const int *__restrict__ radii,
 
 void launch_render_backward(const BwdParams &p, const GeomView &g, const ImageView &im,
                             const BinView &b, cudaStream_t s) {
+  const uint32_t *order = im.tiles <= SPLAT_MAX_ORDERED_TILES ? im.tile_order : nullptr;
   render_backward_kernel<<<im.tiles * SUBS_PER_TILE, 32, 0, s>>>(
-      im.ranges, im.tile_order, b.point_list, reinterpret_cast<const uint16_t *>(b.hdr), b.hdr,
-      g.rec, p.projmatrix, p.W, p.H, im.tiles_x, (uint32_t)p.P, im.final_T, im.n_contrib,
+      im.ranges, order, b.point_list, reinterpret_cast<const uint16_t *>(b.hdr), b.hdr, g.rec, p.projmatrix, p.W, p.H, im.tiles_x, (uint32_t)p.P, im.final_T, im.n_contrib,
       p.dL_dout, p.dL_dtransMat, p.dL_dnormal, p.dL_dopacity);
 }
 

@@ -20,8 +20,6 @@
 // reference's alpha >= 1/255 test at every pixel of the sub-tile, i.e. it is one the
 // reference `continue`s over without touching any state.  `contributor` keeps counting
 // list positions, so n_contrib / median_contributor are the reference's.
-#include <cstdlib>
-
 #include "raster_math.cuh"
 
 namespace {
@@ -211,17 +209,8 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
 
 void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageView &im,
                            const BinView &b, uint32_t capacity, cudaStream_t s) {
-  // experiment knob: extra dynamic shared memory per CTA limits how many warps are resident
-  // per SM, turning the launch into several dynamically scheduled waves
-  static int extra_smem = -1;
-  if (extra_smem < 0) {
-    const char *e = getenv("SPLAT_FWD_SMEM");
-    extra_smem = e ? atoi(e) : 0;
-    if (extra_smem > 48 * 1024)
-      cudaFuncSetAttribute(render_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           extra_smem);
-  }
-  render_forward_kernel<<<im.tiles * SUBS_PER_TILE, 32, extra_smem, s>>>(
-      im.ranges, im.tile_order, b.point_list, b.sub_mask, g.rec, p.projmatrix, p.W, p.H,
-      im.tiles_x, capacity, (uint32_t)p.P, im.final_T, im.n_contrib, p.out_maps);
+  const uint32_t *order = im.tiles <= SPLAT_MAX_ORDERED_TILES ? im.tile_order : nullptr;
+  render_forward_kernel<<<im.tiles * SUBS_PER_TILE, 32, 0, s>>>(
+      im.ranges, order, b.point_list, b.sub_mask, g.rec, p.projmatrix, p.W, p.H, im.tiles_x,
+      capacity, (uint32_t)p.P, im.final_T, im.n_contrib, p.out_maps);
 }

@@ -313,7 +313,7 @@ void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, con
       identify_ranges_kernel<<<blocks, 256, 0, s>>>(&g.hdr->num_rendered, capacity, b.keys,
                                                     im.ranges);
   }
-  if (single < 0)
+  if (single < 0 && im.tiles <= SPLAT_MAX_ORDERED_TILES)   // beyond that: identity order
     tile_order_kernel<<<(im.tiles + 127) / 128, 128, 0, s>>>(im.ranges, im.tiles, im.tile_order);
   if (capacity)
     sub_mask_kernel<<<(capacity + 255) / 256, 256, 0, s>>>(&g.hdr->num_rendered, capacity, b.keys,

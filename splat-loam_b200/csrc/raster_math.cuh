@@ -120,26 +120,6 @@ __device__ __forceinline__ bool intersect_finish(const PixelRay &r, const Surfel
   return true;
 }
 
-// Branch-free form of intersect_finish (same floats, same verdict): lets the compiler
-// interleave two evaluations.  h must come from intersect_begin; lanes for which that
-// returned false may compute garbage here, the caller masks them.
-__device__ __forceinline__ bool intersect_finish_nb(const PixelRay &r, const SurfelRec &s, Hit &h) {
-  h.sx = __fdiv_rn(h.px, h.pz);
-  h.sy = __fdiv_rn(h.py, h.pz);
-  h.rho3d = FF(h.sx, h.sx, FM(h.sy, h.sy));
-  h.bx = FA(s.twx, FF(s.tux, h.sx, FM(s.tvx, h.sy)));
-  h.by = FA(s.twy, FF(s.tuy, h.sx, FM(s.tvy, h.sy)));
-  h.bz = FA(s.twz, FF(s.tuz, h.sx, FM(s.tvz, h.sy)));
-  const float valid = FF(r.Z, h.bz, FF(r.X, h.bx, FM(r.Y, h.by)));
-  const float d3 = __fsqrt_rn(FF(h.bz, h.bz, FF(h.bx, h.bx, FM(h.by, h.by))));
-  h.depth = (h.rho3d <= h.rho2d) ? d3 : s.d2d;
-  const float power = FM(fminf(h.rho3d, h.rho2d), -0.5f);
-  h.G = expf(power);
-  h.alpha = fminf(0.99f, FM(s.opa, h.G));
-  return !(valid < 0.0f) && !(h.depth < SPLAT_NEAR) && !(power > 0.0f) &&
-         !(h.alpha < __uint_as_float(SPLAT_ALPHA_MIN));
-}
-
 // Does the surfel's cull box (see dssr_preprocess.cu:cull_box) touch the pixel
 // rectangle [x0,x1] x [y0,y1]?  x is periodic with the azimuth period.  Written so
 // that any NaN answers "yes".
