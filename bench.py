@@ -41,20 +41,52 @@ def measured_peak_gbs():
 
 
 class ClockSampler:
-    """nvidia-smi clocks and throttle reasons DURING the timed region."""
+    """SM clocks and throttle reasons DURING the timed region.  NVML from a sampling thread
+    (what nvidia-smi reads, without a process spawn or its driver-wide locks every few
+    milliseconds); falls back to `nvidia-smi -lms` when pynvml is missing."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
-    def __init__(self, index):
-        self.rows, self.proc = [], None
+    def __init__(self, index, period_s=0.005):
+        self.rows, self.proc, self.stop_flag, self.source = [], None, False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and vis.split(",")[index].isdigit() else index
+            h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+            bits = [(0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"),
+                    (0x20, "sw_thermal_slowdown"), (0x4, "sw_power_cap")]
+
+            def loop():
+                while not self.stop_flag:
+                    try:
+                        sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                        rs = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h) \
+                            if hasattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons") \
+                            else pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                        self.rows.append([str(sm), str(mx)] +
+                                         ["Active" if rs & b else "Not Active" for b, _ in bits])
+                    except Exception:
+                        pass
+                    time.sleep(period_s)
+            self.t = threading.Thread(target=loop, daemon=True)
+            self.t.start()
+            self.source = "nvml"
+            return
+        except Exception:
+            pass
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}",
-                 "--format=csv,noheader,nounits", "-lms", "20"],
+                 "--format=csv,noheader,nounits", "-lms", "50"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
+            self.source = "nvidia-smi"
         except Exception:
             self.proc = None
 
@@ -63,26 +95,29 @@ class ClockSampler:
             self.rows.append([x.strip() for x in line.split(",")])
 
     def stop(self):
-        if not self.proc:
+        self.stop_flag = True
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+        elif self.source == "nvml":
+            self.t.join(timeout=1)
+        else:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
         sm, mx, reasons = [], None, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        for r in list(self.rows):
             try:
                 sm.append(float(r[0]))
                 mx = float(r[1])
-                for nm, v in zip(names, r[2:6]):
+                for nm, v in zip(self.NAMES, r[2:6]):
                     if v.lower().startswith("active"):
                         reasons.add(nm)
             except Exception:
                 pass
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": self.source}
 
 
 def scene_tensors(cfg, keyframe, device, pinned=False):
@@ -217,22 +252,31 @@ def run_ours(args, rank, world, local_rank):
     rg = _C.debug_state(*bufs, "ranges").numpy()
     Nc = consumed_instances(nc, rg, H, W)
 
-    # ---- device-resident throughput (`value`) + per-stage times ----
-    sampler = ClockSampler(local_rank) if rank == 0 else None
+    # ---- per-stage times (instrumented pass: every stage bracketed by events) ----
     native.profile_enable(True)
+    barrier()
+    nprof = min(args.steps, 20)
+    for _ in range(nprof):
+        flush.zero_()
+        frame(t)
+    torch.cuda.synchronize()
+    stage_ms = {k: v / nprof for k, v in native.profile_read().items()}
+    dom = max(stage_ms, key=stage_ms.get) if stage_ms else "render_backward"
+
+    # ---- device-resident throughput (`value`): only the dominant kernel keeps its event
+    # pair (the roofline's launch duration is measured inside this timed region) ----
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    native.profile_enable(True, only=dom)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
           for _ in range(args.steps)]
-    stages = {}
     barrier()
     for a, b in ev:
         flush.zero_()                     # L2 flush between timed iterations (not timed)
         a.record()
         frame(t)
         b.record()
-        b.synchronize()
-        for k, v in native.profile_read().items():
-            stages[k] = stages.get(k, 0.0) + v
     barrier()
+    dom_ms = native.profile_read().get(dom, 0.0) / args.steps
     native.profile_enable(False)
     total_ms = sum(a.elapsed_time(b) for a, b in ev)
     clocks = sampler.stop() if sampler else None
@@ -270,8 +314,7 @@ def run_ours(args, rank, world, local_rank):
     value = world * 1e3 / ms_per_step
     ab = algorithmic_bytes(P, R, Nc, H * W)
     peak, peak_src = measured_peak_gbs()
-    stage_ms = {k: v / args.steps for k, v in stages.items()}
-    dom = max(stage_ms, key=stage_ms.get) if stage_ms else "render_backward"
+    stage_ms[dom] = dom_ms or stage_ms.get(dom)
     traffic = None
     try:
         traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dom)
@@ -399,7 +442,7 @@ def run_reference(args, rank, world, local_rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="C2", choices=list(scenes.CONFIGS))

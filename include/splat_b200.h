@@ -164,10 +164,13 @@ SPLAT_API int sknn_dist2_static(int P, const float *points, float *mean_dists, v
  * DSSR/tests/test_backward.py:54-85).  While enabled (per host thread), dssr_forward /
  * dssr_backward bracket each stage with CUDA events on the launch stream.  After the
  * caller has synchronised that stream, splat_profile_read returns the stages seen since
- * the last read: their static names and elapsed milliseconds; the return value is the
- * stage count.  Stages: preprocess, emit, sort, render_forward, render_backward,
- * backward_preprocess. */
+ * the last read: their static names and the elapsed milliseconds SUMMED over all calls
+ * since then; the return value is the stage count.  Stages: preprocess, emit, sort,
+ * render_forward, render_backward, backward_preprocess.  splat_profile_select restricts
+ * the bracketing to one stage (NULL: all) - a pair of events costs a few microseconds of
+ * launch overlap, so a throughput measurement instruments only the kernel it reports. */
 SPLAT_API int splat_profile_enable(int on);
+SPLAT_API int splat_profile_select(const char *stage);
 SPLAT_API int splat_profile_read(int max_stages, const char **names, float *ms);
 
 SPLAT_API const char *splat_last_error(void);

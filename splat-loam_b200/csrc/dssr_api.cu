@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <vector>
 
 #include "../../include/splat_b200.h"
 #include "common.cuh"
@@ -54,34 +55,43 @@ struct Trace {
 };
 
 // Optional per-stage device timing (splat_profile_*): CUDA events recorded on the launch
-// stream around each stage, read back by the caller after it has synchronised.
+// stream around each stage (one pair per stage per call, from a growing pool), summed per
+// stage name when the caller reads them back after it has synchronised.
 struct Prof {
-  static constexpr int MAXS = 16;
+  struct Rec {
+    const char *name;
+    cudaEvent_t beg, end;
+  };
   bool on = false;
-  int n = 0;
-  cudaEvent_t beg[MAXS], end[MAXS];
-  const char *name[MAXS];
-  bool made = false;
-  int slot(const char *nm) {
-    for (int i = 0; i < n; i++)
-      if (name[i] == nm) return i;
-    if (n == MAXS) return -1;
-    name[n] = nm;
-    return n++;
+  std::string only;        // empty: every stage
+  std::vector<Rec> pool;   // events are created once and reused
+  size_t used = 0;
+  Rec *take(const char *nm) {
+    if (!on || (!only.empty() && only != nm)) return nullptr;
+    if (used == pool.size()) {
+      Rec r{nm, nullptr, nullptr};
+      if (cudaEventCreate(&r.beg) != cudaSuccess) return nullptr;
+      if (cudaEventCreate(&r.end) != cudaSuccess) {
+        cudaEventDestroy(r.beg);
+        return nullptr;
+      }
+      pool.push_back(r);
+    }
+    Rec *r = &pool[used++];
+    r->name = nm;
+    return r;
   }
 };
 thread_local Prof g_prof;
 
 struct ProfScope {
-  int s = -1;
+  Prof::Rec *r;
   cudaStream_t st;
-  ProfScope(const char *nm, cudaStream_t st_) : st(st_) {
-    if (!g_prof.on) return;
-    s = g_prof.slot(nm);
-    if (s >= 0) cudaEventRecord(g_prof.beg[s], st);
+  ProfScope(const char *nm, cudaStream_t st_) : r(g_prof.take(nm)), st(st_) {
+    if (r) cudaEventRecord(r->beg, st);
   }
   ~ProfScope() {
-    if (s >= 0) cudaEventRecord(g_prof.end[s], st);
+    if (r) cudaEventRecord(r->end, st);
   }
 };
 
@@ -137,7 +147,7 @@ int splat_fail(const char *fmt, ...) {
 extern "C" {
 
 const char *splat_last_error(void) { return g_err.c_str(); }
-int splat_abi_version(void) { return 2; }
+int splat_abi_version(void) { return 3; }
 
 size_t dssr_geometry_bytes(int P) { return GeomLayout(P < 0 ? 0 : P).total; }
 size_t dssr_image_bytes(int W, int H) { return ImageLayout(W, H).total; }
@@ -148,28 +158,33 @@ size_t dssr_binning_bytes(int64_t capacity, int W, int H, int P, int keep_unsort
 }
 
 int splat_profile_enable(int on) {
-  if (on && !g_prof.made) {
-    for (int i = 0; i < Prof::MAXS; i++) {
-      if (cudaEventCreate(&g_prof.beg[i]) != cudaSuccess ||
-          cudaEventCreate(&g_prof.end[i]) != cudaSuccess)
-        return fail("splat_profile_enable: cudaEventCreate failed");
-    }
-    g_prof.made = true;
-  }
   g_prof.on = on != 0;
-  g_prof.n = 0;
+  g_prof.used = 0;
+  return 0;
+}
+
+int splat_profile_select(const char *stage) {
+  g_prof.only = stage ? stage : "";
   return 0;
 }
 
 int splat_profile_read(int max_stages, const char **names, float *ms) {
-  int n = g_prof.n < max_stages ? g_prof.n : max_stages;
-  for (int i = 0; i < n; i++) {
+  int n = 0;
+  for (size_t i = 0; i < g_prof.used; i++) {
+    const Prof::Rec &r = g_prof.pool[i];
     float t = 0.f;
-    if (cudaEventElapsedTime(&t, g_prof.beg[i], g_prof.end[i]) != cudaSuccess) t = -1.f;
-    if (names) names[i] = g_prof.name[i];
-    if (ms) ms[i] = t;
+    if (cudaEventElapsedTime(&t, r.beg, r.end) != cudaSuccess) t = -1.f;
+    int k = 0;
+    while (k < n && names[k] != r.name) k++;   // stage names are string literals
+    if (k == n) {
+      if (n == max_stages) continue;
+      names[n] = r.name;
+      ms[n] = 0.f;
+      n++;
+    }
+    if (t < 0.f || ms[k] < 0.f) ms[k] = -1.f; else ms[k] += t;
   }
-  g_prof.n = 0;
+  g_prof.used = 0;
   return n;
 }
 

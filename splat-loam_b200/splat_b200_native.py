@@ -54,7 +54,7 @@ EXPORTS = (
     "dssr_forward", "dssr_backward", "dssr_mark_visible", "dssr_geometry_bytes",
     "dssr_image_bytes", "dssr_binning_bytes", "dssr_debug_state", "sknn_workspace_bytes",
     "sknn_dist2", "splat_last_error", "splat_abi_version", "splat_profile_enable",
-    "splat_profile_read", "sknn_dist2_static",
+    "splat_profile_read", "splat_profile_select", "sknn_dist2_static",
 )
 
 _lib = None
@@ -102,6 +102,8 @@ def load():
     lib.splat_abi_version.restype = ctypes.c_int
     lib.splat_profile_enable.argtypes = [ctypes.c_int]
     lib.splat_profile_enable.restype = ctypes.c_int
+    lib.splat_profile_select.argtypes = [ctypes.c_char_p]
+    lib.splat_profile_select.restype = ctypes.c_int
     lib.splat_profile_read.argtypes = [ctypes.c_int, ctypes.POINTER(ctypes.c_char_p),
                                        ctypes.POINTER(ctypes.c_float)]
     lib.splat_profile_read.restype = ctypes.c_int
@@ -109,12 +111,14 @@ def load():
     return lib
 
 
-def profile_enable(on=True):
+def profile_enable(on=True, only=None):
+    """Bracket every stage (or just `only`) of the calling thread's frames with CUDA events."""
+    check(load().splat_profile_select(only.encode() if only else None))
     check(load().splat_profile_enable(int(bool(on))))
 
 
 def profile_read():
-    """{stage: milliseconds} for the stages run since the last read (synchronise first)."""
+    """{stage: milliseconds summed over the calls since the last read} (synchronise first)."""
     names = (ctypes.c_char_p * 16)()
     ms = (ctypes.c_float * 16)()
     n = load().splat_profile_read(16, names, ms)
