@@ -227,6 +227,14 @@ def run_ours(args, rank, world, local_rank):
     gbuf = torch.empty((P, 10), dtype=torch.float32, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB of L2
 
+    # keyframe-sharded window: the [P,10] gradients are summed over the ranks through NVLink
+    # peer memory, the push half fused into the per-surfel VJP kernel (SPLAT_B200_XCHG=nccl:
+    # one NCCL all-reduce instead)
+    xchg = None
+    if world > 1 and os.environ.get("SPLAT_B200_XCHG", "peer") != "nccl":
+        from keyframe_window import PeerExchange
+        xchg = PeerExchange(P, dev)
+
     def frame(x):
         R, allmap, radii, geom, binning, img = _C.rasterize_gaussians(
             x["means3D"], x["opacities"], x["scales"], x["rotations"], 1.0, empty,
@@ -234,8 +242,11 @@ def run_ours(args, rank, world, local_rank):
         # the [P,10] packed gradients come straight out of the per-surfel VJP kernel
         g = _C.rasterize_gaussians_backward(
             x["means3D"], radii, x["scales"], x["rotations"], 1.0, empty, x["viewmatrix"],
-            x["projmatrix"], x["dL_dout"], geom, R, binning, img, False, packed=gbuf)
-        if world > 1:   # keyframe-sharded window: one all-reduce of the [P,10] buffer
+            x["projmatrix"], x["dL_dout"], geom, R, binning, img, False,
+            packed=None if xchg else gbuf, xchg=xchg.handle.value if xchg else None)
+        if xchg:
+            xchg.allreduce()
+        elif world > 1:
             dist.all_reduce(gbuf)
         return R, allmap, g, (geom, binning, img)
 
@@ -292,8 +303,11 @@ def run_ours(args, rank, world, local_rank):
             x["viewmatrix"], x["projmatrix"], H, W, False, False)
         _C.rasterize_gaussians_backward(
             x["means3D"], radii, x["scales"], x["rotations"], 1.0, empty, x["viewmatrix"],
-            x["projmatrix"], x["dL_dout"], geom, R, binning, img, False, packed=gbufs[slot])
-        if world > 1:
+            x["projmatrix"], x["dL_dout"], geom, R, binning, img, False,
+            packed=None if xchg else gbufs[slot], xchg=xchg.handle.value if xchg else None)
+        if xchg:      # the exchange owns ONE result array: park it in this step's slot
+            gbufs[slot].copy_(xchg.allreduce())
+        elif world > 1:
             dist.all_reduce(gbufs[slot])
         return [allmap, gbufs[slot]]
 
@@ -327,13 +341,17 @@ def run_ours(args, rank, world, local_rank):
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.config}: {H}x{W} spherical range image, {P} surfels, "
                                f"fwd+bwd per frame, one keyframe per GPU"
-                               + (", NCCL all-reduce of the [P,10] gradients" if world > 1 else ""),
+                               + ((", [P,10] gradients summed over NVLink peer memory (push "
+                                   "fused into the VJP kernel)" if xchg else
+                                   ", NCCL all-reduce of the [P,10] gradients")
+                                  if world > 1 else ""),
                    "instances": R, "consumed_instances": Nc,
                    "l2": "256 MB buffer written between timed steps",
                    "parallelism": f"keyframe-sharded x{world}"},
         "e2e": {"value": world * 1e3 / (e2e_ms / args.steps), "unit": UNIT,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-        "gpu_launches": 12 * args.steps,   # 10 forward + 2 backward kernels per frame
+        # 10 forward + 2 backward kernels per frame (+ reduce and wait of the exchange)
+        "gpu_launches": (14 if xchg else 12) * args.steps,
         "stage_ms": stage_ms,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak,
                      "peak_source": peak_src, "unit": "GB/s",

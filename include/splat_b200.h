@@ -102,6 +102,12 @@ typedef struct {
    * all of its keyframes into it without any extra kernel. */
   float *packed_grads;
   int packed_accumulate;
+  /* Optional (NULL = off): a connected gradient exchange (splat_xchg_*, below).  The
+   * per-surfel VJP kernel then also stores every [10] row - plus, with packed_accumulate,
+   * what packed_grads held - into the staging slot of the rank that owns the row, over
+   * NVLink, while it computes: the reduce-scatter half of the window all-reduce costs no
+   * kernel and no extra pass over HBM.  Follow with splat_xchg_allreduce. */
+  struct splat_xchg *xchg;
   void *stream;
 } dssr_backward_args;
 
@@ -158,6 +164,34 @@ SPLAT_API int sknn_dist2(int P, const float *points, float *mean_dists, void *wo
  *   - no cudaMalloc, cudaFree or allocating library routine is called. */
 #define SKNN_STATIC_MAX_POINTS 65536
 SPLAT_API int sknn_dist2_static(int P, const float *points, float *mean_dists, void *stream);
+
+/* ---- keyframe-window gradient exchange over NVLink peer memory -------------------
+ * No counterpart in the reference (it maps on one GPU, slam/mapper.py:150-156).  One
+ * process per GPU; every rank creates an exchange for the same P and world, the ranks swap
+ * the 64-byte handles (any transport: torch.distributed, MPI, a file) and connect.  Then
+ * per optimisation step:
+ *     dssr_backward(... xchg ...)   or   splat_xchg_push(x, packed [P,10] or NULL = zeros)
+ *     splat_xchg_allreduce(x, stream)          (= splat_xchg_reduce + splat_xchg_wait)
+ * after which splat_xchg_result(x) - a [P,10] device array owned by the exchange - holds the
+ * sum over ranks, bit-identical on every rank (each row is summed once, by its owner, in
+ * rank order).  Work is ordered by `stream`; the kernels wait for peers through flags in
+ * peer memory and give up after ~2 s (reported by the next splat_xchg_* call).  All ranks
+ * must make the same sequence of calls.  world <= 16; peers must be NVLink/P2P reachable.
+ * splat_xchg_connect_local wires exchanges that live in ONE process (tests, or a process
+ * driving several GPUs); with it, when several ranks share a stream, issue every rank's
+ * reduce before any rank's wait. */
+#define SPLAT_XCHG_HANDLE_BYTES 64
+typedef struct splat_xchg splat_xchg;
+SPLAT_API int splat_xchg_create(int P, int world, int rank, splat_xchg **out);
+SPLAT_API int splat_xchg_export(splat_xchg *x, unsigned char *handle /* [64] */);
+SPLAT_API int splat_xchg_connect(splat_xchg *x, const unsigned char *handles /* [world][64] */);
+SPLAT_API int splat_xchg_connect_local(splat_xchg *x, splat_xchg *const *peers /* [world] */);
+SPLAT_API int splat_xchg_push(splat_xchg *x, const float *packed, void *stream);
+SPLAT_API int splat_xchg_reduce(splat_xchg *x, void *stream);
+SPLAT_API int splat_xchg_wait(splat_xchg *x, void *stream);
+SPLAT_API int splat_xchg_allreduce(splat_xchg *x, void *stream);
+SPLAT_API float *splat_xchg_result(splat_xchg *x);
+SPLAT_API int splat_xchg_destroy(splat_xchg *x);
 
 /* ---- per-stage device timing ----------------------------------------------------
  * No counterpart in the reference (its only timing is wall-clock prints in

@@ -19,6 +19,7 @@ SOURCES = [
     "dssr_render_fwd.cu",
     "dssr_render_bwd.cu",
     "sknn.cu",
+    "peer_exchange.cu",
 ]
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-lineinfo",

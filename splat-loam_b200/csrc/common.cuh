@@ -300,6 +300,7 @@ struct BwdParams {
       *dL_dscales, *dL_drotations;
   float *packed;          // optional [P,10]
   int packed_accumulate;
+  const struct XchgView *push;   // optional fused push into the window exchange
 };
 void launch_render_backward(const BwdParams &p, const GeomView &g, const ImageView &im,
                             const BinView &b, cudaStream_t s);

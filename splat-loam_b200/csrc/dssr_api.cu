@@ -12,6 +12,7 @@
 
 #include "../../include/splat_b200.h"
 #include "common.cuh"
+#include "peer_exchange.cuh"
 
 static thread_local std::string g_err;
 
@@ -147,7 +148,7 @@ int splat_fail(const char *fmt, ...) {
 extern "C" {
 
 const char *splat_last_error(void) { return g_err.c_str(); }
-int splat_abi_version(void) { return 3; }
+int splat_abi_version(void) { return 4; }
 
 size_t dssr_geometry_bytes(int P) { return GeomLayout(P < 0 ? 0 : P).total; }
 size_t dssr_image_bytes(int W, int H) { return ImageLayout(W, H).total; }
@@ -303,6 +304,12 @@ int dssr_backward(const dssr_backward_args *a) {
   bp.dL_drotations = a->dL_drotations;
   bp.packed = a->packed_grads;
   bp.packed_accumulate = a->packed_accumulate;
+  XchgView xv;
+  bp.push = nullptr;
+  if (a->xchg) {
+    if (xchg_begin_push(a->xchg, a->P, &xv)) return 1;
+    bp.push = &xv;
+  }
   {
     ProfScope ps("render_backward", st);
     launch_render_backward(bp, gv, iv, bv, st);

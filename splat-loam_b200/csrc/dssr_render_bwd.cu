@@ -14,6 +14,7 @@
 // 15-shuffle transposed butterfly, after which 13 lanes issue ONE atomic instruction
 // (one RED per component per sub-tile instead of one per pixel).  The reference's backward is not the adjoint of its forward (SURVEY.md §8 a10,
 // quirks Q1-Q4, Q7); it is reproduced as written.
+#include "peer_exchange.cuh"
 #include "raster_math.cuh"
 
 namespace {
@@ -314,6 +315,10 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
 
 // Per-surfel VJP: dL/dT, dL/dnormal -> dL/dmean3D, dL/dscale, dL/dquat.
 // Writes every output element (zeros for culled surfels) so no memset is needed.
+// PUSH: the [10] row also goes to the staging slot of the rank that owns it (NVLink store)
+// and the last CTA publishes this rank's arrival to all peers - the reduce-scatter half of the
+// window all-reduce, overlapped row by row with the arithmetic above it.
+template <bool PUSH>
 __global__ void __launch_bounds__(256)
 backward_preprocess_kernel(int P, const int *__restrict__ radii,
                            const float *__restrict__ scales,
@@ -323,12 +328,14 @@ backward_preprocess_kernel(int P, const int *__restrict__ radii,
                            const float *__restrict__ dL_dnormal,
                            const float *__restrict__ dL_dopacity, float *dL_dmeans3D,
                            float *dL_dscales, float *dL_drot, float *packed,
-                           int packed_accumulate) {
+                           int packed_accumulate, XchgView xv) {
+  static_assert(XCHG_SLICE_ALIGN == 256, "one CTA = one 256-row block with a single owner");
+  __shared__ __align__(16) float s_rows[PUSH ? XCHG_SLICE_ALIGN * XCHG_ROW : 4];
   __shared__ float m[16];
   if (threadIdx.x < 16) m[threadIdx.x] = viewmatrix[threadIdx.x];
   __syncthreads();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= P) return;
+  if (idx < P) {
   float3 dmean = make_float3(0.f, 0.f, 0.f);
   float2 dscale = make_float2(0.f, 0.f);
   float4 dq = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -388,16 +395,33 @@ backward_preprocess_kernel(int P, const int *__restrict__ radii,
   dL_dmeans3D[3 * (size_t)idx + 2] = dmean.z;
   reinterpret_cast<float2 *>(dL_dscales)[idx] = dscale;
   reinterpret_cast<float4 *>(dL_drot)[idx] = dq;
-  if (packed) {   // [means3D 3 | opacity 1 | scales 2 | rotations 4]
-    float2 *row = reinterpret_cast<float2 *>(packed + 10 * (size_t)idx);
+  if (packed || PUSH) {   // [means3D 3 | opacity 1 | scales 2 | rotations 4]
     float2 r0 = make_float2(dmean.x, dmean.y), r1 = make_float2(dmean.z, dL_dopacity[idx]),
            r2 = dscale, r3 = make_float2(dq.x, dq.y), r4 = make_float2(dq.z, dq.w);
-    if (packed_accumulate) {
-      const float2 o0 = row[0], o1 = row[1], o2 = row[2], o3 = row[3], o4 = row[4];
-      r0.x += o0.x; r0.y += o0.y; r1.x += o1.x; r1.y += o1.y; r2.x += o2.x; r2.y += o2.y;
-      r3.x += o3.x; r3.y += o3.y; r4.x += o4.x; r4.y += o4.y;
+    if (packed) {
+      float2 *row = reinterpret_cast<float2 *>(packed + 10 * (size_t)idx);
+      if (packed_accumulate) {
+        const float2 o0 = row[0], o1 = row[1], o2 = row[2], o3 = row[3], o4 = row[4];
+        r0.x += o0.x; r0.y += o0.y; r1.x += o1.x; r1.y += o1.y; r2.x += o2.x; r2.y += o2.y;
+        r3.x += o3.x; r3.y += o3.y; r4.x += o4.x; r4.y += o4.y;
+      }
+      row[0] = r0; row[1] = r1; row[2] = r2; row[3] = r3; row[4] = r4;
     }
-    row[0] = r0; row[1] = r1; row[2] = r2; row[3] = r3; row[4] = r4;
+    if (PUSH) {
+      float2 *row = reinterpret_cast<float2 *>(s_rows + XCHG_ROW * threadIdx.x);
+      row[0] = r0; row[1] = r1; row[2] = r2; row[3] = r3; row[4] = r4;
+    }
+  }
+  }
+  if (PUSH) {
+    const int row0 = blockIdx.x * blockDim.x;
+    if (idx >= P) {
+      float2 *row = reinterpret_cast<float2 *>(s_rows + XCHG_ROW * threadIdx.x);
+      row[0] = row[1] = row[2] = row[3] = row[4] = make_float2(0.f, 0.f);
+    }
+    __syncthreads();
+    xchg_store_block(xv, row0, min((int)blockDim.x, P - row0), s_rows);
+    xchg_publish(xv, 0);
   }
 }
 
@@ -412,8 +436,14 @@ void launch_render_backward(const BwdParams &p, const GeomView &g, const ImageVi
 }
 
 void launch_backward_preprocess(const BwdParams &p, cudaStream_t s) {
-  backward_preprocess_kernel<<<(p.P + 255) / 256, 256, 0, s>>>(
-      p.P, p.radii, p.scales, p.rotations, p.viewmatrix, p.dL_dtransMat, p.dL_dnormal,
-      p.dL_dopacity, p.dL_dmeans3D, p.dL_dscales, p.dL_drotations, p.packed,
-      p.packed_accumulate);
+  if (p.push)
+    backward_preprocess_kernel<true><<<(p.P + 255) / 256, 256, 0, s>>>(
+        p.P, p.radii, p.scales, p.rotations, p.viewmatrix, p.dL_dtransMat, p.dL_dnormal,
+        p.dL_dopacity, p.dL_dmeans3D, p.dL_dscales, p.dL_drotations, p.packed,
+        p.packed_accumulate, *p.push);
+  else
+    backward_preprocess_kernel<false><<<(p.P + 255) / 256, 256, 0, s>>>(
+        p.P, p.radii, p.scales, p.rotations, p.viewmatrix, p.dL_dtransMat, p.dL_dnormal,
+        p.dL_dopacity, p.dL_dmeans3D, p.dL_dscales, p.dL_drotations, p.packed,
+        p.packed_accumulate, XchgView());
 }

@@ -102,11 +102,13 @@ def rasterize_gaussians(means3D, opacity, scales, rotations, scale_modifier, tra
 def rasterize_gaussians_backward(means3D, radii, scales, rotations, scale_modifier,
                                  transMat_precomp, viewmatrix, projmatrix, dL_dout, geomBuffer,
                                  R, binningBuffer, imageBuffer, debug, packed=None,
-                                 packed_accumulate=False):
+                                 packed_accumulate=False, xchg=None):
     """Reference signature (rasterize_points.cu:90-147).  Extension: `packed`, a contiguous
     float32 [P,10] tensor that additionally receives (or, with packed_accumulate, is
     incremented by) dL_dmeans3D | dL_dopacity | dL_dscales | dL_drotations - the message of
-    the keyframe-window all-reduce."""
+    the keyframe-window all-reduce; `xchg`, the handle of a connected peer exchange
+    (keyframe_window.PeerExchange): the same rows are pushed to their owner ranks by the VJP
+    kernel itself."""
     for t, nm in ((means3D, "means3D"), (radii, "radii"), (scales, "scales"),
                   (rotations, "rotations"), (transMat_precomp, "transMat_precomp"),
                   (viewmatrix, "viewmatrix"), (projmatrix, "projmatrix"),
@@ -143,7 +145,7 @@ def rasterize_gaussians_backward(means3D, radii, scales, rotations, scale_modifi
                 _ptr(dmeans2D), _ptr(dnormal), _ptr(dopacity), _ptr(dmeans3D), _ptr(dtrans),
                 _ptr(dscales), _ptr(drot),
                 _ptr(packed) if packed is not None else None, int(bool(packed_accumulate)),
-                torch.cuda.current_stream(dev).cuda_stream)
+                xchg, torch.cuda.current_stream(dev).cuda_stream)
             _n.check(_lib.dssr_backward(ctypes.byref(a)))
     return dmeans2D, dopacity, dmeans3D, dtrans, dscales, drot
 

@@ -45,6 +45,7 @@ class DssrBackwardArgs(ctypes.Structure):
         ("dL_dmeans3D", c_float_p), ("dL_dtransMat", c_float_p), ("dL_dscales", c_float_p),
         ("dL_drotations", c_float_p),
         ("packed_grads", c_float_p), ("packed_accumulate", ctypes.c_int),
+        ("xchg", ctypes.c_void_p),
         ("stream", ctypes.c_void_p),
     ]
 
@@ -55,7 +56,11 @@ EXPORTS = (
     "dssr_image_bytes", "dssr_binning_bytes", "dssr_debug_state", "sknn_workspace_bytes",
     "sknn_dist2", "splat_last_error", "splat_abi_version", "splat_profile_enable",
     "splat_profile_read", "splat_profile_select", "sknn_dist2_static",
+    "splat_xchg_create", "splat_xchg_export", "splat_xchg_connect", "splat_xchg_connect_local",
+    "splat_xchg_push", "splat_xchg_reduce", "splat_xchg_wait", "splat_xchg_allreduce",
+    "splat_xchg_result", "splat_xchg_destroy",
 )
+XCHG_HANDLE_BYTES = 64
 
 _lib = None
 
@@ -107,6 +112,21 @@ def load():
     lib.splat_profile_read.argtypes = [ctypes.c_int, ctypes.POINTER(ctypes.c_char_p),
                                        ctypes.POINTER(ctypes.c_float)]
     lib.splat_profile_read.restype = ctypes.c_int
+    vp = ctypes.c_void_p
+    lib.splat_xchg_create.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(vp)]
+    lib.splat_xchg_export.argtypes = [vp, ctypes.c_char_p]
+    lib.splat_xchg_connect.argtypes = [vp, ctypes.c_char_p]
+    lib.splat_xchg_connect_local.argtypes = [vp, ctypes.POINTER(vp)]
+    lib.splat_xchg_push.argtypes = [vp, c_float_p, vp]
+    for f in (lib.splat_xchg_reduce, lib.splat_xchg_wait, lib.splat_xchg_allreduce):
+        f.argtypes = [vp, vp]
+    lib.splat_xchg_result.argtypes = [vp]
+    lib.splat_xchg_result.restype = vp
+    lib.splat_xchg_destroy.argtypes = [vp]
+    for f in (lib.splat_xchg_create, lib.splat_xchg_export, lib.splat_xchg_connect,
+              lib.splat_xchg_connect_local, lib.splat_xchg_push, lib.splat_xchg_reduce,
+              lib.splat_xchg_wait, lib.splat_xchg_allreduce, lib.splat_xchg_destroy):
+        f.restype = ctypes.c_int
     _lib = lib
     return lib
 
