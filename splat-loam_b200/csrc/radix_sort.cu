@@ -274,6 +274,13 @@ unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long
                                        int unpack_last, int idx_bits, int nblk,
                                        cudaStream_t s) {
   unsigned long long *src = a, *dst = b;
+  static bool attr_set = false;
+  if (!attr_set) {   // the widest pass (10 bits) needs more than the default 48 KB
+    const int big = WARPS * SORT_MAX_BINS * 2 + SORT_MAX_BINS * 4;
+    cudaFuncSetAttribute(sort_pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
+    cudaFuncSetAttribute(sort_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
+    attr_set = true;
+  }
   for (int p = 0; p < npass; p++) {
     const int nbins = 1 << bits[p];
     const size_t smem = (size_t)WARPS * nbins * 2 + (size_t)nbins * 4;
