@@ -362,9 +362,46 @@ def run_ours(args, rank, world, local_rank):
                            "frac": ab["frame"] / (ms_per_step * 1e-3) / 1e9 / peak},
         "clocks": clocks,
     }
+    if world == 1:
+        line["post"] = post_stage(allmap.detach(), t)
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args.config)
     return line
+
+
+def post_stage(allmap, t, iters=50):
+    """SURVEY.md §8(f) rank 1, reported beside the headline: render()'s map post-processing,
+    forward + backward, as the fused kernel pair (gaussian_renderer.postprocess) and as the
+    reference's own sequence of PyTorch ops (the oracle's torch restatement, which reproduces
+    the reference's render() to 1e-7) on the same GPU.  CUDA events, after warm-up."""
+    import gaussian_renderer as gr
+    from oracle import render_post as rp
+    V, Pm = t["viewmatrix"], t["projmatrix"]
+    g = {k: torch.randn(s, device=allmap.device) for k, s in
+         (("rend_alpha", allmap[1:2].shape), ("rend_normal", allmap[2:5].shape),
+          ("rend_dist", allmap[6:7].shape), ("surf_depth", allmap[0:1].shape),
+          ("surf_normal", allmap[2:5].shape))}
+
+    def step(fn):
+        a = allmap.clone().requires_grad_(True)
+        out = fn(a, V, Pm, 0.0)
+        torch.autograd.backward([out[k] for k in g], [g[k] for k in g])
+        return a.grad
+
+    res = {}
+    for name, fn in (("fused_ms", gr.postprocess), ("torch_ops_ms", rp.post_forward)):
+        for _ in range(5):
+            step(fn)
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            step(fn)
+        b.record()
+        b.synchronize()
+        res[name] = a.elapsed_time(b) / iters
+    res["what"] = "render() map post-processing fwd+bwd per frame (incl. clone + autograd glue)"
+    return res
 
 
 # ------------------------------------------------------------------ baselines ----------

@@ -119,6 +119,39 @@ SPLAT_API int dssr_mark_visible(int P, const float *means3D, const float *viewma
                       const float *projmatrix, unsigned char *present,
                       void *stream);
 
+/* ---- map post-processing of render() (the caller side) --------
+ * Replaces what gaussian_renderer/__init__.py:51-92 and utils/graphic_utils.py:26-88
+ * (depth_to_points, depth_to_normal) do to the rasterizer's [7,H,W] output with ~25 PyTorch
+ * kernels forward and ~50 backward, by one kernel per direction:
+ *   rend_normal [3,H,W] = world_view_transform[:3,:3] . normal map, / alpha where alpha > 0
+ *   surf_depth  [1,H,W] = (depth / alpha where alpha > 0)(1 - depth_ratio) + median depth * depth_ratio
+ *   surf_normal [3,H,W] = alpha * normalised cross product of the central differences of the
+ *                         back-projected surf_depth (zero on the one-pixel border)
+ * rend_alpha and rend_dist of render() are channels 1 and 6 of allmap itself.  viewmatrix /
+ * projmatrix are the camera's world_view_transform / projection_matrix (device, 16 floats).
+ * The backward takes the upstream gradients of the three maps (any may be NULL = zero) and
+ * writes dL/dallmap [7,H,W] in full (channel 6 = 0; add the gradients that reach channels
+ * 1 and 6 directly through rend_alpha / rend_dist yourself, as autograd does for views). */
+typedef struct {
+  int W, H;
+  float depth_ratio;
+  const float *allmap;
+  const float *viewmatrix, *projmatrix;
+  float *rend_normal, *surf_depth, *surf_normal;
+  void *stream;
+} dssr_post_forward_args;
+typedef struct {
+  int W, H;
+  float depth_ratio;
+  const float *allmap;
+  const float *viewmatrix, *projmatrix;
+  const float *dL_drend_normal, *dL_dsurf_depth, *dL_dsurf_normal;
+  float *dL_dallmap;
+  void *stream;
+} dssr_post_backward_args;
+SPLAT_API int dssr_post_forward(const dssr_post_forward_args *args);
+SPLAT_API int dssr_post_backward(const dssr_post_backward_args *args);
+
 /* Buffer sizes the callbacks will be asked for (mirrors required<T>(),
  * DSSR/cuda_rasterizer/rasterizer_impl.h:59-64). */
 SPLAT_API size_t dssr_geometry_bytes(int P);

@@ -20,6 +20,7 @@ SOURCES = [
     "dssr_render_bwd.cu",
     "sknn.cu",
     "peer_exchange.cu",
+    "render_post.cu",
 ]
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-lineinfo",

@@ -50,6 +50,25 @@ class DssrBackwardArgs(ctypes.Structure):
     ]
 
 
+class DssrPostForwardArgs(ctypes.Structure):
+    _fields_ = [
+        ("W", ctypes.c_int), ("H", ctypes.c_int), ("depth_ratio", ctypes.c_float),
+        ("allmap", c_float_p), ("viewmatrix", c_float_p), ("projmatrix", c_float_p),
+        ("rend_normal", c_float_p), ("surf_depth", c_float_p), ("surf_normal", c_float_p),
+        ("stream", ctypes.c_void_p),
+    ]
+
+
+class DssrPostBackwardArgs(ctypes.Structure):
+    _fields_ = [
+        ("W", ctypes.c_int), ("H", ctypes.c_int), ("depth_ratio", ctypes.c_float),
+        ("allmap", c_float_p), ("viewmatrix", c_float_p), ("projmatrix", c_float_p),
+        ("dL_drend_normal", c_float_p), ("dL_dsurf_depth", c_float_p),
+        ("dL_dsurf_normal", c_float_p), ("dL_dallmap", c_float_p),
+        ("stream", ctypes.c_void_p),
+    ]
+
+
 # every symbol include/splat_b200.h declares
 EXPORTS = (
     "dssr_forward", "dssr_backward", "dssr_mark_visible", "dssr_geometry_bytes",
@@ -58,7 +77,7 @@ EXPORTS = (
     "splat_profile_read", "splat_profile_select", "sknn_dist2_static",
     "splat_xchg_create", "splat_xchg_export", "splat_xchg_connect", "splat_xchg_connect_local",
     "splat_xchg_push", "splat_xchg_reduce", "splat_xchg_wait", "splat_xchg_allreduce",
-    "splat_xchg_result", "splat_xchg_destroy",
+    "splat_xchg_result", "splat_xchg_destroy", "dssr_post_forward", "dssr_post_backward",
 )
 XCHG_HANDLE_BYTES = 64
 
@@ -112,6 +131,10 @@ def load():
     lib.splat_profile_read.argtypes = [ctypes.c_int, ctypes.POINTER(ctypes.c_char_p),
                                        ctypes.POINTER(ctypes.c_float)]
     lib.splat_profile_read.restype = ctypes.c_int
+    lib.dssr_post_forward.argtypes = [ctypes.POINTER(DssrPostForwardArgs)]
+    lib.dssr_post_forward.restype = ctypes.c_int
+    lib.dssr_post_backward.argtypes = [ctypes.POINTER(DssrPostBackwardArgs)]
+    lib.dssr_post_backward.restype = ctypes.c_int
     vp = ctypes.c_void_p
     lib.splat_xchg_create.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(vp)]
     lib.splat_xchg_export.argtypes = [vp, ctypes.c_char_p]
