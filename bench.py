@@ -401,6 +401,35 @@ def post_stage(allmap, t, iters=50):
         b.synchronize()
         res[name] = a.elapsed_time(b) / iters
     res["what"] = "render() map post-processing fwd+bwd per frame (incl. clone + autograd glue)"
+
+    # the same with the mapper's image losses on top (slam/mapper.py:158-195)
+    import mapping_loss as ml
+
+    class Cam:
+        world_view_transform, projection_matrix = V, Pm
+        image_depth = (allmap[5:6] + 0.1).contiguous()
+        image_valid = (allmap[1:2] > 0).to(torch.uint8)
+
+    def fused_loss():
+        a = allmap.clone().requires_grad_(True)
+        ml.mapping_image_losses(a, Cam, 0.0, 0.1, 0.1)["total"].backward()
+
+    def torch_loss():
+        a = allmap.clone().requires_grad_(True)
+        pkg = rp.post_forward(a, V, Pm, 0.0)
+        rp.mapper_image_losses(pkg, Cam.image_depth, Cam.image_valid, 0.1, 0.1)[3].backward()
+
+    for name, fn in (("fused_with_losses_ms", fused_loss), ("torch_ops_with_losses_ms", torch_loss)):
+        for _ in range(5):
+            fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record()
+        b.synchronize()
+        res[name] = a.elapsed_time(b) / iters
     return res
 
 

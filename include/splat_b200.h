@@ -152,6 +152,49 @@ typedef struct {
 SPLAT_API int dssr_post_forward(const dssr_post_forward_args *args);
 SPLAT_API int dssr_post_backward(const dssr_post_backward_args *args);
 
+/* The same two kernels with the mapper's per-keyframe image losses folded in
+ * (slam/mapper.py:158-190; inline code there, no function to mirror):
+ *   losses[0] geom_l1 = mean over H*W of |valid (surf_depth - gt_depth)|
+ *   losses[1] normal  = lambda_normal * mean over valid of (1 - <rend_normal, surf_normal>)
+ *   losses[2] alpha   = lambda_alpha * mean over valid of BCE(rend_alpha, 1)
+ *   losses[3] total   = [0] + [2] + [1]        losses[4] = number of valid pixels
+ * with valid <=> gt_valid == 1 (camera.image_valid, uint8).  The forward never writes the maps
+ * unless asked to (rend_normal / surf_depth / surf_normal may be NULL); the backward derives
+ * the maps' upstream gradients from the loss definition instead of reading them, and takes
+ * dL_dlosses (device, 5 floats, or NULL = d total only) so nothing is synchronised with the
+ * host.  `workspace`: DSSR_POST_LOSS_WORKSPACE_BYTES device bytes, 8-byte aligned, zeroed once
+ * by the caller; every launch leaves it zeroed.  The scale regulariser of mapper.py:186-191
+ * acts on the parameters, not on the image, and stays with the caller. */
+#define DSSR_POST_LOSS_WORKSPACE_BYTES 64
+typedef struct {
+  int W, H;
+  float depth_ratio;
+  const float *allmap;
+  const float *viewmatrix, *projmatrix;
+  const float *gt_depth;             /* [H,W] camera.image_depth                     */
+  const unsigned char *gt_valid;     /* [H,W] camera.image_valid                     */
+  float lambda_normal, lambda_alpha;
+  float *rend_normal, *surf_depth, *surf_normal;   /* optional map outputs           */
+  float *losses;                     /* [5] device                                   */
+  void *workspace;
+  void *stream;
+} dssr_post_loss_forward_args;
+typedef struct {
+  int W, H;
+  float depth_ratio;
+  const float *allmap;
+  const float *viewmatrix, *projmatrix;
+  const float *gt_depth;
+  const unsigned char *gt_valid;
+  float lambda_normal, lambda_alpha;
+  const float *losses;               /* [5] from the forward                         */
+  const float *dL_dlosses;           /* [5] device, or NULL                          */
+  float *dL_dallmap;                 /* [7,H,W], written in full                     */
+  void *stream;
+} dssr_post_loss_backward_args;
+SPLAT_API int dssr_post_loss_forward(const dssr_post_loss_forward_args *args);
+SPLAT_API int dssr_post_loss_backward(const dssr_post_loss_backward_args *args);
+
 /* Buffer sizes the callbacks will be asked for (mirrors required<T>(),
  * DSSR/cuda_rasterizer/rasterizer_impl.h:59-64). */
 SPLAT_API size_t dssr_geometry_bytes(int P);

@@ -64,6 +64,22 @@ def post_forward(allmap, world_view_transform, projection_matrix, depth_ratio=0.
             "surf_depth": surf_depth[None], "surf_normal": surf_normal}
 
 
+def mapper_image_losses(pkg, gt_depth, gt_alpha, lambda_normal, lambda_alpha):
+    """The per-keyframe image losses of the mapping loop, as written in slam/mapper.py:158-195
+    (inline code there; `gt_alpha` is camera.image_valid, uint8 [1,H,W]; `gt_depth`
+    camera.image_depth [1,H,W]).  Returns (geom_l1, normal_loss, alpha_loss, total)."""
+    est_alpha, est_depth = pkg["rend_alpha"], pkg["surf_depth"]
+    est_normal, surf_normal = pkg["rend_normal"], pkg["surf_normal"]
+    valid = gt_alpha[0] == 1.0                                               # :166
+    geom_l1 = torch.abs(valid * (est_depth - gt_depth)).mean()               # :174-175
+    cos = (est_normal[..., valid] * surf_normal[..., valid]).sum(dim=0)      # :177-179
+    normal_loss = (1 - cos).mean() * lambda_normal                           # :177-180
+    alpha_loss = torch.nn.functional.binary_cross_entropy(                   # :182-186
+        est_alpha[..., valid], gt_alpha[..., valid].to(est_alpha.dtype), reduction="mean")
+    alpha_loss = alpha_loss * lambda_alpha                                   # :187
+    return geom_l1, normal_loss, alpha_loss, geom_l1 + alpha_loss + normal_loss   # :193-195
+
+
 OUTPUTS = ("rend_alpha", "rend_normal", "rend_dist", "surf_depth", "surf_normal")
 
 

@@ -69,6 +69,30 @@ class DssrPostBackwardArgs(ctypes.Structure):
     ]
 
 
+class DssrPostLossForwardArgs(ctypes.Structure):
+    _fields_ = [
+        ("W", ctypes.c_int), ("H", ctypes.c_int), ("depth_ratio", ctypes.c_float),
+        ("allmap", c_float_p), ("viewmatrix", c_float_p), ("projmatrix", c_float_p),
+        ("gt_depth", c_float_p), ("gt_valid", ctypes.c_void_p),
+        ("lambda_normal", ctypes.c_float), ("lambda_alpha", ctypes.c_float),
+        ("rend_normal", c_float_p), ("surf_depth", c_float_p), ("surf_normal", c_float_p),
+        ("losses", c_float_p), ("workspace", ctypes.c_void_p), ("stream", ctypes.c_void_p),
+    ]
+
+
+class DssrPostLossBackwardArgs(ctypes.Structure):
+    _fields_ = [
+        ("W", ctypes.c_int), ("H", ctypes.c_int), ("depth_ratio", ctypes.c_float),
+        ("allmap", c_float_p), ("viewmatrix", c_float_p), ("projmatrix", c_float_p),
+        ("gt_depth", c_float_p), ("gt_valid", ctypes.c_void_p),
+        ("lambda_normal", ctypes.c_float), ("lambda_alpha", ctypes.c_float),
+        ("losses", c_float_p), ("dL_dlosses", c_float_p), ("dL_dallmap", c_float_p),
+        ("stream", ctypes.c_void_p),
+    ]
+
+
+POST_LOSS_WORKSPACE_BYTES = 64
+
 # every symbol include/splat_b200.h declares
 EXPORTS = (
     "dssr_forward", "dssr_backward", "dssr_mark_visible", "dssr_geometry_bytes",
@@ -78,6 +102,7 @@ EXPORTS = (
     "splat_xchg_create", "splat_xchg_export", "splat_xchg_connect", "splat_xchg_connect_local",
     "splat_xchg_push", "splat_xchg_reduce", "splat_xchg_wait", "splat_xchg_allreduce",
     "splat_xchg_result", "splat_xchg_destroy", "dssr_post_forward", "dssr_post_backward",
+    "dssr_post_loss_forward", "dssr_post_loss_backward",
 )
 XCHG_HANDLE_BYTES = 64
 
@@ -135,6 +160,10 @@ def load():
     lib.dssr_post_forward.restype = ctypes.c_int
     lib.dssr_post_backward.argtypes = [ctypes.POINTER(DssrPostBackwardArgs)]
     lib.dssr_post_backward.restype = ctypes.c_int
+    lib.dssr_post_loss_forward.argtypes = [ctypes.POINTER(DssrPostLossForwardArgs)]
+    lib.dssr_post_loss_forward.restype = ctypes.c_int
+    lib.dssr_post_loss_backward.argtypes = [ctypes.POINTER(DssrPostLossBackwardArgs)]
+    lib.dssr_post_loss_backward.restype = ctypes.c_int
     vp = ctypes.c_void_p
     lib.splat_xchg_create.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(vp)]
     lib.splat_xchg_export.argtypes = [vp, ctypes.c_char_p]

@@ -88,6 +88,31 @@ def case(render, state, allmap, view, proj, depth_ratio, seed):
     return g
 
 
+def loss_case(render, state, allmap, view, proj, depth_ratio, seed, lam_n, lam_a):
+    """render() is the reference's; the 12 loss lines of slam/mapper.py:158-195 have no callable
+    boundary there (inline in Mapper.optimize), so they are evaluated through the restatement
+    oracle/render_post.mapper_image_losses (the torch primitives are the reference's)."""
+    from oracle import render_post as rp
+    H, W = allmap.shape[1:]
+    state["allmap"] = torch.from_numpy(allmap.copy()).requires_grad_(True)
+    state["radii"] = torch.ones(4, dtype=torch.int32)
+    pkg = render(Cam(view, proj, H, W), Model(4), depth_ratio)
+    rng = np.random.default_rng(seed)
+    gt_depth = (pkg["surf_depth"].detach().numpy() + 0.2 * rng.standard_normal((1, H, W))).astype(np.float32)
+    gt_depth[0, rng.uniform(size=(H, W)) < 0.02] = pkg["surf_depth"].detach().numpy()[0].mean()
+    gt_valid = (rng.uniform(size=(1, H, W)) < 0.8).astype(np.uint8)
+    gt_valid[0][allmap[1] <= 0] = 0        # BCE of alpha == 0 is the -100 clamp: kept out of the
+    gt_valid[0, :2, :5] = 1                # mean except for this deliberate corner
+    losses = rp.mapper_image_losses(pkg, torch.from_numpy(gt_depth), torch.from_numpy(gt_valid),
+                                    lam_n, lam_a)
+    losses[3].backward()
+    return {"allmap": allmap, "viewmatrix": view, "projmatrix": proj,
+            "depth_ratio": np.float32(depth_ratio), "gt_depth": gt_depth, "gt_valid": gt_valid,
+            "lambda_normal": np.float32(lam_n), "lambda_alpha": np.float32(lam_a),
+            "losses": np.array([float(x.detach()) for x in losses], dtype=np.float64),
+            "dL_dallmap": state["allmap"].grad.numpy()}
+
+
 def rasterized_map(cfg, keyframe):
     s = scenes.make_scene(cfg, keyframe=keyframe)
     oracle.build()
@@ -120,8 +145,13 @@ def main(outdir):
     np.savez_compressed(os.path.join(outdir, "post_c0.npz"), **case(render, state, m, view, proj, 0.0, 1))
     np.savez_compressed(os.path.join(outdir, "post_c0_ratio.npz"),
                         **case(render, state, m, view, proj, 0.3, 2))
+    np.savez_compressed(os.path.join(outdir, "post_loss_c0.npz"),
+                        **loss_case(render, state, m, view, proj, 0.0, 11, 0.1, 0.1))
     H, W = 24, 80
     proj = scenes.intrinsics(H, W, 40.0)
+    np.savez_compressed(os.path.join(outdir, "post_loss_synth.npz"),
+                        **loss_case(render, state, synthetic_map(H, W, 8), scenes.viewmatrix(3),
+                                    proj, 0.4, 12, 0.05, 0.5))
     view = scenes.viewmatrix(3)
     np.savez_compressed(os.path.join(outdir, "post_synth.npz"),
                         **case(render, state, synthetic_map(H, W, 5), view, proj, 1.0, 3))

@@ -54,3 +54,22 @@ def test_border_and_empty_pixels():
     assert hole.any() and not sn[:, hole].any()
     lens = np.linalg.norm(sn[:, 1:-1, 1:-1], axis=0)
     np.testing.assert_allclose(lens, g["allmap"][1][1:-1, 1:-1], atol=1e-5)
+
+
+@pytest.mark.parametrize("name", ("post_loss_c0", "post_loss_synth"))
+def test_loss_restatement_against_golden(name):
+    """The loss goldens come from the reference's render() + the restated loss lines in fp32;
+    re-evaluated here in fp32 (must reproduce) and fp64 (the tolerance the CUDA path gets)."""
+    g = load_golden(name)
+    for dtype, tol_l, tol_g in ((torch.float32, 1e-6, 1e-6), (torch.float64, 1e-5, 1e-4)):
+        a, V, Pm, r = _inputs(g, dtype)
+        a.requires_grad_(True)
+        pkg = rp.post_forward(a, V, Pm, r)
+        losses = rp.mapper_image_losses(pkg, torch.from_numpy(g["gt_depth"]).to(dtype),
+                                        torch.from_numpy(g["gt_valid"]),
+                                        float(g["lambda_normal"]), float(g["lambda_alpha"]))
+        for got, want in zip(losses, g["losses"]):
+            assert abs(float(got.detach()) - want) <= tol_l * max(1.0, abs(want))
+        losses[3].backward()
+        ref = torch.from_numpy(g["dL_dallmap"]).to(dtype)
+        assert float((a.grad - ref).norm() / ref.norm()) < tol_g
