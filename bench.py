@@ -364,9 +364,66 @@ def run_ours(args, rank, world, local_rank):
     }
     if world == 1:
         line["post"] = post_stage(allmap.detach(), t)
+        line["optimizer"] = adam_stage(P, dev)
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args.config)
     return line
+
+
+def adam_stage(P, dev, iters=50):
+    """SURVEY.md §8(f) rank 2, reported beside the headline: from the [P,10] gradients to
+    updated parameters.  `torch_ms`: what the reference runs (activations, autograd through
+    them and the scale regulariser, torch.optim.Adam.step); `fused_ms`: the same activations
+    (for the next frame's rasterizer call) + ONE kernel (fused_adam.activation_adam_step)."""
+    from fused_adam import activation_adam_step
+    g = torch.Generator(device=dev).manual_seed(1)
+    raw = {"xyz": torch.randn(P, 3, device=dev, generator=g),
+           "opacity": torch.randn(P, 1, device=dev, generator=g),
+           "scaling": torch.randn(P, 2, device=dev, generator=g) - 1.0,
+           "rotation": torch.randn(P, 4, device=dev, generator=g)}
+    G = torch.randn(P, 10, device=dev, generator=g)
+    lrs = {"xyz": 1.6e-4, "opacity": 5e-2, "scaling": 5e-3, "rotation": 1e-3}
+
+    def make():
+        ps = {k: torch.nn.Parameter(v.clone()) for k, v in raw.items()}
+        return ps, torch.optim.Adam([{"params": [ps[k]], "lr": lrs[k], "name": k} for k in ps],
+                                    lr=0.0, eps=1e-15)
+
+    def acts(ps):
+        return (ps["xyz"], torch.sigmoid(ps["opacity"]), torch.exp(ps["scaling"]),
+                torch.nn.functional.normalize(ps["rotation"]))
+
+    pa, oa = make()
+    pb, ob = make()
+
+    def torch_step():
+        oa.zero_grad(set_to_none=True)
+        a = acts(pa)
+        smax = a[2].max(dim=1).values
+        reg = (0.2 * (smax[smax >= 0.5] - 0.5)).sum()
+        torch.autograd.backward(list(a) + [reg], [G[:, 0:3], G[:, 3:4], G[:, 4:6], G[:, 6:10],
+                                                  torch.ones_like(reg)])
+        oa.step()
+
+    def fused_step():
+        with torch.no_grad():
+            acts(pb)
+        activation_adam_step(ob, G, 0.5, 0.2)
+
+    res = {}
+    for name, fn in (("fused_ms", fused_step), ("torch_ms", torch_step)):
+        for _ in range(5):
+            fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record()
+        b.synchronize()
+        res[name] = a.elapsed_time(b) / iters
+    res["what"] = f"activations + their backward + scale regulariser + Adam, P={P}"
+    return res
 
 
 def post_stage(allmap, t, iters=50):

@@ -195,6 +195,29 @@ typedef struct {
 SPLAT_API int dssr_post_loss_forward(const dssr_post_loss_forward_args *args);
 SPLAT_API int dssr_post_loss_backward(const dssr_post_loss_backward_args *args);
 
+/* ---- activation backward + Adam in one pass -----------------
+ * Replaces, for the four parameter groups of scene/gaussian_model.py:97-121 (xyz, opacity,
+ * scaling, rotation - arrays indexed in that order below): autograd's backward through the
+ * activations (gaussian_model.py:58-74: identity, sigmoid, exp, F.normalize), the backward of
+ * the scale regulariser (slam/mapper.py:186-191; scaling_max_penalty = 0 turns it off) and
+ * torch.optim.Adam.step() (no weight decay, no amsgrad).  `packed_grads` is the [P,10] buffer
+ * of dssr_backward / splat_xchg_result: gradients w.r.t. the ACTIVATED values.  param /
+ * exp_avg / exp_avg_sq are the raw parameters and the optimizer's state tensors, updated in
+ * place; step[k] is the step count AFTER this update (>= 1), as torch increments it first.
+ * reg_out (optional, device float) is incremented by the regulariser's value. */
+typedef struct {
+  int P;
+  const float *packed_grads;
+  float *param[4], *exp_avg[4], *exp_avg_sq[4];
+  double lr[4];
+  long long step[4];
+  double beta1, beta2, eps;
+  double scaling_max, scaling_max_penalty;
+  float *reg_out;
+  void *stream;
+} splat_adam_args;
+SPLAT_API int splat_activation_adam_step(const splat_adam_args *args);
+
 /* Buffer sizes the callbacks will be asked for (mirrors required<T>(),
  * DSSR/cuda_rasterizer/rasterizer_impl.h:59-64). */
 SPLAT_API size_t dssr_geometry_bytes(int P);

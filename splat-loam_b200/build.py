@@ -21,6 +21,7 @@ SOURCES = [
     "sknn.cu",
     "peer_exchange.cu",
     "render_post.cu",
+    "adam_step.cu",
 ]
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-lineinfo",

@@ -148,7 +148,7 @@ int splat_fail(const char *fmt, ...) {
 extern "C" {
 
 const char *splat_last_error(void) { return g_err.c_str(); }
-int splat_abi_version(void) { return 6; }
+int splat_abi_version(void) { return 7; }
 
 size_t dssr_geometry_bytes(int P) { return GeomLayout(P < 0 ? 0 : P).total; }
 size_t dssr_image_bytes(int W, int H) { return ImageLayout(W, H).total; }

@@ -91,6 +91,17 @@ class DssrPostLossBackwardArgs(ctypes.Structure):
     ]
 
 
+class SplatAdamArgs(ctypes.Structure):
+    _fields_ = [
+        ("P", ctypes.c_int), ("packed_grads", c_float_p),
+        ("param", c_float_p * 4), ("exp_avg", c_float_p * 4), ("exp_avg_sq", c_float_p * 4),
+        ("lr", ctypes.c_double * 4), ("step", ctypes.c_longlong * 4),
+        ("beta1", ctypes.c_double), ("beta2", ctypes.c_double), ("eps", ctypes.c_double),
+        ("scaling_max", ctypes.c_double), ("scaling_max_penalty", ctypes.c_double),
+        ("reg_out", c_float_p), ("stream", ctypes.c_void_p),
+    ]
+
+
 POST_LOSS_WORKSPACE_BYTES = 64
 
 # every symbol include/splat_b200.h declares
@@ -102,7 +113,7 @@ EXPORTS = (
     "splat_xchg_create", "splat_xchg_export", "splat_xchg_connect", "splat_xchg_connect_local",
     "splat_xchg_push", "splat_xchg_reduce", "splat_xchg_wait", "splat_xchg_allreduce",
     "splat_xchg_result", "splat_xchg_destroy", "dssr_post_forward", "dssr_post_backward",
-    "dssr_post_loss_forward", "dssr_post_loss_backward",
+    "dssr_post_loss_forward", "dssr_post_loss_backward", "splat_activation_adam_step",
 )
 XCHG_HANDLE_BYTES = 64
 
@@ -164,6 +175,8 @@ def load():
     lib.dssr_post_loss_forward.restype = ctypes.c_int
     lib.dssr_post_loss_backward.argtypes = [ctypes.POINTER(DssrPostLossBackwardArgs)]
     lib.dssr_post_loss_backward.restype = ctypes.c_int
+    lib.splat_activation_adam_step.argtypes = [ctypes.POINTER(SplatAdamArgs)]
+    lib.splat_activation_adam_step.restype = ctypes.c_int
     vp = ctypes.c_void_p
     lib.splat_xchg_create.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(vp)]
     lib.splat_xchg_export.argtypes = [vp, ctypes.c_char_p]
