@@ -225,7 +225,7 @@ def run_ours(args, rank, world, local_rank):
     H, W, P = t["H"], t["W"], t["means3D"].shape[0]
     empty = torch.empty(0, device=dev)
     gbuf = torch.empty((P, 10), dtype=torch.float32, device=dev)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB of L2
+    flush = torch.empty(192 << 20, dtype=torch.uint8, device=dev)   # > 126 MB of L2
 
     # keyframe-sharded window: the [P,10] gradients are summed over the ranks through NVLink
     # peer memory, the push half fused into the per-surfel VJP kernel (SPLAT_B200_XCHG=nccl:
@@ -346,7 +346,7 @@ def run_ours(args, rank, world, local_rank):
                                    ", NCCL all-reduce of the [P,10] gradients")
                                   if world > 1 else ""),
                    "instances": R, "consumed_instances": Nc,
-                   "l2": "256 MB buffer written between timed steps",
+                   "l2": "192 MB buffer (1.5x the 126 MB L2) written between timed steps",
                    "parallelism": f"keyframe-sharded x{world}"},
         "e2e": {"value": world * 1e3 / (e2e_ms / args.steps), "unit": UNIT,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
@@ -532,7 +532,7 @@ def run_reference(args, rank, world, local_rank):
     H, W, P = t["H"], t["W"], t["means3D"].shape[0]
     opa = t["opacities"].reshape(-1).contiguous()
     ref = reflib.RefRasterizer()
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    flush = torch.empty(192 << 20, dtype=torch.uint8, device=dev)
 
     def frame(x, o):
         R, out, radii = ref.forward(x["means3D"], o, x["scales"], x["rotations"],
@@ -571,7 +571,7 @@ def run_reference(args, rank, world, local_rank):
         value=1e3 / ms, ms_per_step=ms,
         config={"workload": f"{args.config}: {H}x{W}, {P} surfels, fwd+bwd per frame, UNMODIFIED "
                             "reference CUDA rasterizer (oracle/_ref), 1 GPU",
-                "l2": "256 MB buffer written between timed steps"},
+                "l2": "192 MB buffer (1.5x the 126 MB L2) written between timed steps"},
         kind="reference",
         e2e={"value": 1e3 / ms_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d,
              "d2h_bytes_per_step": d2h})
