@@ -32,8 +32,9 @@
 #define PRE_CHUNK 256             // surfels per preprocess block (one thread each)
 
 #define SORT_THREADS 512
-#define SORT_ITEMS 16                                  // keys per thread per pass
-#define SORT_BLOCK_ELEMS (SORT_THREADS * SORT_ITEMS)   // 8192
+#define SORT_ITEMS 16                                  // keys per thread per pass: 8, 12 or 16
+#define SORT_BLOCK_ELEMS (SORT_THREADS * SORT_ITEMS)   // 8192 (largest CTA chunk)
+#define SORT_MIN_BLOCK_ELEMS (SORT_THREADS * 8)        // smallest chunk: sizes the status arrays
 #define SORT_MAX_BINS 1024
 #define SORT_MAX_PASSES 6
 #define HIST_REPL 32              // replicas of the global digit histograms
@@ -131,7 +132,7 @@ struct BinLayout {
   size_t status_off[SORT_MAX_PASSES];  // element offset of each pass in `status`
   int nblk;
   __host__ BinLayout(size_t C, int keep_unsorted, const SortPlan &sp) {
-    nblk = (int)((C + SORT_BLOCK_ELEMS - 1) / SORT_BLOCK_ELEMS);
+    nblk = (int)((C + SORT_MIN_BLOCK_ELEMS - 1) / SORT_MIN_BLOCK_ELEMS);
     if (nblk < 1) nblk = 1;
     size_t o = align_up(sizeof(BinHeader), 256);
     // point_list first: its offset must not depend on the capacity, the backward
@@ -270,7 +271,7 @@ void launch_emit(const FwdParams &p, const GeomView &g, const ImageView &im,
                  const BinView &b, const SortPlan &sp, uint32_t capacity,
                  cudaStream_t s);
 void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, const BinView &b,
-                 const SortPlan &sp, uint32_t capacity, cudaStream_t s);
+                 const SortPlan &sp, uint32_t capacity, uint32_t n_estimate, cudaStream_t s);
 void launch_digit_scan(const uint32_t *hist, uint32_t *digit_base, int npass, uint2 *ranges,
                        uint32_t *tile_order, int tiles, int tile_pass_single, int nrepl,
                        cudaStream_t s);
@@ -286,8 +287,9 @@ unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long
                                        uint32_t *status, const size_t *status_off,
                                        uint32_t *tickets, const uint32_t *digit_base,
                                        int npass, const int *shift, const int *bits,
-                                       int unpack_last, int idx_bits, int nblk,
-                                       cudaStream_t s);
+                                       int unpack_last, int idx_bits, uint32_t n_estimate,
+                                       cudaStream_t s, const MaskParams *mp = nullptr,
+                                       uint32_t P = 0);
 void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageView &im,
                            const BinView &b, uint32_t capacity, cudaStream_t s);
 

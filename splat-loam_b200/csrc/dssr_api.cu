@@ -21,6 +21,7 @@ namespace {
 thread_local uint32_t *g_pinned = nullptr;      // 2 words: num_rendered, status (mapped)
 thread_local uint32_t *g_pinned_dev = nullptr;  // the device's view of g_pinned
 thread_local cudaEvent_t g_event = nullptr;
+thread_local uint32_t g_last_count = 0;         // num_rendered of this thread's previous forward
 
 #define fail splat_fail
 
@@ -107,7 +108,7 @@ int ensure_host_scratch() {
 
 int run_binning_and_render(const dssr_forward_args *a, const FwdParams &fp,
                            const GeomView &gv, const ImageView &iv, const SortPlan &sp,
-                           uint32_t capacity, cudaStream_t st) {
+                           uint32_t capacity, uint32_t n_estimate, cudaStream_t st) {
   const int keep = (a->debug & 2) ? 1 : 0;
   const bool dbg = a->debug & 1;
   BinLayout bl(capacity, keep, sp);
@@ -122,7 +123,7 @@ int run_binning_and_render(const dssr_forward_args *a, const FwdParams &fp,
   LAUNCH_CHECK(dbg, st, "emit");
   {
     ProfScope ps("sort", st);
-    launch_sort(fp, gv, iv, bv, sp, capacity, st);
+    launch_sort(fp, gv, iv, bv, sp, capacity, n_estimate, st);
   }
   LAUNCH_CHECK(dbg, st, "sort");
   {
@@ -250,8 +251,12 @@ int dssr_forward(const dssr_forward_args *a, int *num_rendered) {
   // the instance count (the reference blocks here: rasterizer_impl.cu:216-219).
   int64_t hint = a->binning_hint;
   if (hint > 0x3fffffff) hint = 0x3fffffff;
+  // (the sort sizes its CTAs for the number of instances it expects: the previous frame's
+  // count of this thread when that fits the hint, else the hint itself)
   if (hint > 0)
-    if (run_binning_and_render(a, fp, gv, iv, sp, (uint32_t)hint, st)) return 1;
+    if (run_binning_and_render(a, fp, gv, iv, sp, (uint32_t)hint,
+                               g_last_count && g_last_count <= hint ? g_last_count : (uint32_t)hint, st))
+      return 1;
   tr.lap("enqueue binning (hint)");
   CUDA_TRY(cudaEventSynchronize(g_event));
   tr.lap("wait for count");
@@ -259,8 +264,9 @@ int dssr_forward(const dssr_forward_args *a, int *num_rendered) {
   if (status & 1u)
     return fail("Point is filtered although prefiltered is set. This shouldn't happen!");
   if (N > 0x3fffffffu) return fail("dssr_forward: %u instances exceed the 2^30 limit", N);
+  g_last_count = N;
   if (hint <= 0 || (int64_t)N > hint)
-    if (run_binning_and_render(a, fp, gv, iv, sp, N, st)) return 1;
+    if (run_binning_and_render(a, fp, gv, iv, sp, N, N, st)) return 1;
   tr.lap("enqueue binning (exact)");
   *num_rendered = (int)N;
   return 0;

@@ -104,29 +104,6 @@ __global__ void identify_ranges_kernel(const uint32_t *num_ptr, uint32_t capacit
   if (i == L - 1) ranges[cur].y = L;
 }
 
-// sub_mask[i]: which 4x4 sub-tiles of its tile the i-th sorted instance's cull box can touch
-// (consumed by the compositing kernels instead of re-testing boxes in their inner loops).
-__global__ void __launch_bounds__(256)
-sub_mask_kernel(const uint32_t *__restrict__ num_ptr, uint32_t capacity,
-                const unsigned long long *__restrict__ keys,
-                const uint32_t *__restrict__ point_list, MaskParams mp, uint32_t P) {
-  const uint32_t N = min(*num_ptr, capacity);
-  const uint32_t i = blockIdx.x * 256 + threadIdx.x;
-  if (i >= N) return;
-  const float fx = mp.projmatrix[0], fy = mp.projmatrix[5], cy = mp.projmatrix[9];
-  const float inv_period = 1.0f / (6.2831853f * fabsf(fx));
-  // culling assumes |elevation| < pi/2 on every image row
-  const bool cull_on = fmaxf(fabsf((0.0f - cy) / fy), fabsf(((float)(mp.H - 1) - cy) / fy)) < 1.55f;
-  uint32_t sm = 0xffffu;
-  if (cull_on) {
-    const uint32_t t = (uint32_t)(keys[i] >> 32);
-    const uint32_t id = min(point_list[i], P - 1u);
-    sm = subtile_mask(mp.cull[id], (float)((t % mp.tiles_x) * SPLAT_TILE),
-                      (float)((t / mp.tiles_x) * SPLAT_TILE), inv_period);
-  }
-  mp.sub_mask[i] = (uint16_t)sm;
-}
-
 // tile_order[rank] = tile, rank by decreasing list length (ties by index): the compositing
 // kernels number their CTAs through it so that long and short lists are spread evenly.
 __global__ void tile_order_kernel(const uint2 *__restrict__ ranges, int tiles,
@@ -145,16 +122,15 @@ __global__ void tile_order_kernel(const uint2 *__restrict__ ranges, int tiles,
 }
 
 // One radix pass.  Each CTA takes a ticket (so CTA b only ever waits on CTAs that
-// have already started), ranks its 4096 words stably per digit with warp match-any,
+// have already started), ranks its 512 x ITEMS words stably per digit with warp match-any,
 // publishes its digit counts, resolves its global offsets by looking back over the
 // predecessors' published counts, and scatters.
-template <bool LAST>
+template <int ITEMS>
 __global__ void __launch_bounds__(SORT_THREADS)
 sort_pass_kernel(const unsigned long long *__restrict__ in, unsigned long long *out,
-                 unsigned long long *keys_out, uint32_t *plist_out,
                  const uint32_t *__restrict__ num_ptr, uint32_t capacity, uint32_t *status,
                  uint32_t *ticket, const uint32_t *__restrict__ digit_base, int shift,
-                 int bits, int idx_bits) {
+                 int bits) {
   extern __shared__ uint32_t smem[];
   const int bins = 1 << bits;
   uint16_t *s_cnt = reinterpret_cast<uint16_t *>(smem);            // [WARPS][bins]
@@ -166,22 +142,22 @@ sort_pass_kernel(const unsigned long long *__restrict__ in, unsigned long long *
   for (int i = tid; i < (WARPS * bins) / 2; i += SORT_THREADS) smem[i] = 0u;
   __syncthreads();
   const uint32_t bid = s_bid;
-  const uint32_t start = bid * SORT_BLOCK_ELEMS;
+  const uint32_t start = bid * (SORT_THREADS * ITEMS);
   if (start >= N) return;
 
   const uint32_t mask = (uint32_t)bins - 1u;
   const uint32_t lt = (1u << lane) - 1u;
-  unsigned long long key[SORT_ITEMS];
-  uint16_t rank[SORT_ITEMS];
+  unsigned long long key[ITEMS];
+  uint16_t rank[ITEMS];
   uint16_t *my_cnt = s_cnt + wid * bins;
-  const uint32_t wstart = start + wid * (SORT_ITEMS * 32);
+  const uint32_t wstart = start + wid * (ITEMS * 32);
 #pragma unroll
-  for (int r = 0; r < SORT_ITEMS; r++) {
+  for (int r = 0; r < ITEMS; r++) {
     uint32_t i = wstart + r * 32 + lane;
     key[r] = (i < N) ? in[i] : ~0ull;
   }
 #pragma unroll
-  for (int r = 0; r < SORT_ITEMS; r++) {
+  for (int r = 0; r < ITEMS; r++) {
     uint32_t i = wstart + r * 32 + lane;
     bool valid = i < N;
     uint32_t digit = valid ? ((uint32_t)(key[r] >> shift) & mask) : 0xffffffffu;
@@ -231,29 +207,244 @@ sort_pass_kernel(const unsigned long long *__restrict__ in, unsigned long long *
   }
   __syncthreads();
 
-  const unsigned long long idx_mask = (1ull << idx_bits) - 1ull;
 #pragma unroll
-  for (int r = 0; r < SORT_ITEMS; r++) {
+  for (int r = 0; r < ITEMS; r++) {
     uint32_t i = wstart + r * 32 + lane;
     if (i < N) {
       uint32_t digit = (uint32_t)(key[r] >> shift) & mask;
       uint32_t pos = s_base[digit] + my_cnt[digit] + rank[r];
       if (pos >= capacity) continue;  // only when the capacity hint was too small
-      if (LAST) {
-        unsigned long long k = key[r];
-        uint32_t idx = (uint32_t)(k & idx_mask);
-        uint32_t d27 = (uint32_t)(k >> idx_bits) & ((1u << SPLAT_DEPTH_BITS) - 1u);
-        unsigned long long tile = k >> (idx_bits + SPLAT_DEPTH_BITS);
-        keys_out[pos] = (tile << 32) | (unsigned long long)(d27 + SPLAT_DEPTH_BASE);
-        plist_out[pos] = idx;
-      } else {
-        out[pos] = key[r];
-      }
+      out[pos] = key[r];
     }
   }
 }
 
+// Developer facility (build with -DSORT_TRACE, read with tests/dev_sort_trace.py): wall-clock
+// timestamps of the phases of every CTA of the last pass.
+#ifdef SORT_TRACE
+__device__ unsigned long long g_trace[1024][16];
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define TRACE(slot) if (threadIdx.x == 0 && bid < 1024) g_trace[bid][slot] = gtime();
+#else
+#define TRACE(slot)
+#endif
+
+// The final pass of the rasterizer's sort (the tile digit): same chained scan, but
+//   * ranking by ballots - on tile digits MATCH.ANY was measured ~3x slower than on the
+//     depth digits (its cost depends on the group structure of the operands);
+//   * the CTA's words are first put in CTA-sorted order in shared memory and written out
+//     from there, so consecutive threads store consecutive addresses: the direct scatter
+//     of this pass ran at a fifth of the store rate of the depth passes;
+//   * the unpacking to the reference's point_list_keys / point_list and the 16-bit
+//     sub-tile mask of every instance (previously a kernel of its own that re-read the keys)
+//     are done on the way out.
+template <int ITEMS>
+__global__ void __launch_bounds__(SORT_THREADS)
+sort_last_pass_kernel(const unsigned long long *__restrict__ in,
+                      unsigned long long *__restrict__ keys_out, uint32_t *__restrict__ plist_out,
+                      MaskParams mp, uint32_t P, const uint32_t *__restrict__ num_ptr,
+                      uint32_t capacity, uint32_t *status, uint32_t *ticket,
+                      const uint32_t *__restrict__ digit_base, int shift, int bits, int idx_bits) {
+  extern __shared__ uint32_t smem[];
+  const int bins = 1 << bits;
+  uint16_t *s_cnt = reinterpret_cast<uint16_t *>(smem);            // [WARPS][bins]
+  uint32_t *s_base = smem + (WARPS * bins) / 2;                    // [bins] CTA total, then delta
+  uint32_t *s_loc = s_base + bins;                                 // [bins] CTA-local exclusive
+  unsigned long long *s_stage =
+      reinterpret_cast<unsigned long long *>(s_loc + bins);        // [(SORT_THREADS * ITEMS)]
+  __shared__ uint32_t s_bid;
+  __shared__ uint32_t s_warp[WARPS];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const uint32_t N = min(*num_ptr, capacity);
+  if (tid == 0) s_bid = atomicAdd(ticket, 1u);
+  for (int i = tid; i < (WARPS * bins) / 2; i += SORT_THREADS) smem[i] = 0u;
+  __syncthreads();
+  const uint32_t bid = s_bid;
+  const uint32_t start = bid * (SORT_THREADS * ITEMS);
+  if (start >= N) return;
+  const uint32_t count = min((uint32_t)(SORT_THREADS * ITEMS), N - start);
+  TRACE(0)
+
+  const uint32_t mask = (uint32_t)bins - 1u;
+  const uint32_t lt = (1u << lane) - 1u;
+  unsigned long long key[ITEMS];
+  uint16_t rank[ITEMS];
+  uint16_t *my_cnt = s_cnt + wid * bins;
+  const uint32_t wstart = start + wid * (ITEMS * 32);
+#pragma unroll
+  for (int r = 0; r < ITEMS; r++) {
+    uint32_t i = wstart + r * 32 + lane;
+    key[r] = (i < N) ? in[i] : ~0ull;
+  }
+#ifdef SORT_TRACE
+  {
+    unsigned long long acc = 0;
+#pragma unroll
+    for (int r = 0; r < ITEMS; r++) acc ^= key[r];
+    if (acc == 0xdeadbeefdeadbeefull) g_trace[0][15] = acc;
+    __syncthreads();
+    TRACE(8)
+  }
+#endif
+#pragma unroll
+  for (int r = 0; r < ITEMS; r++) {
+    const uint32_t i = wstart + r * 32 + lane;
+    const bool valid = i < N;
+    const uint32_t digit = (uint32_t)(key[r] >> shift) & mask;
+    uint32_t peers = __ballot_sync(0xffffffffu, valid);
+    peers = valid ? peers : ~peers;
+#pragma unroll
+    for (int b = 0; b < 10; b++) {          // SORT_MAX_BINS = 1024
+      if (b < bits) {
+        const bool bit = (digit >> b) & 1u;
+        const uint32_t m = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? m : ~m;
+      }
+    }
+    const int leader = __ffs(peers) - 1;
+    uint32_t old = 0;
+    if (lane == leader && valid) {
+      old = my_cnt[digit];
+      my_cnt[digit] = (uint16_t)(old + __popc(peers));
+    }
+    old = __shfl_sync(0xffffffffu, old, leader);
+    rank[r] = (uint16_t)(old + __popc(peers & lt));
+    __syncwarp();
+  }
+  __syncthreads();
+  TRACE(1)
+
+  // per digit: exclusive prefix over the warps, CTA total, publish
+  uint32_t *my_status = status + (size_t)bid * bins;
+  for (int d = tid; d < bins; d += SORT_THREADS) {
+    uint32_t run = 0;
+#pragma unroll
+    for (int w = 0; w < WARPS; w++) {
+      uint32_t c = s_cnt[w * bins + d];
+      s_cnt[w * bins + d] = (uint16_t)run;
+      run += c;
+    }
+    s_base[d] = run;
+    st_volatile_u32(&my_status[d], (bid == 0 ? FLAG_INCL : FLAG_LOCAL) | run);
+  }
+  __syncthreads();
+  TRACE(2)
+  // CTA-local exclusive scan of the totals over the digits (thread t owns bins [t*ipt, ..))
+  {
+    const int ipt = (bins + SORT_THREADS - 1) / SORT_THREADS;     // 1 or 2
+    const int d0 = tid * ipt;
+    const uint32_t v0 = d0 < bins ? s_base[d0] : 0u;
+    const uint32_t v1 = (ipt > 1 && d0 + 1 < bins) ? s_base[d0 + 1] : 0u;
+    uint32_t inc = v0 + v1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += n;
+    }
+    if (lane == 31) s_warp[wid] = inc;
+    __syncthreads();
+    uint32_t before = 0;
+    for (int w = 0; w < wid; w++) before += s_warp[w];
+    const uint32_t excl = before + inc - (v0 + v1);
+    if (d0 < bins) s_loc[d0] = excl;
+    if (ipt > 1 && d0 + 1 < bins) s_loc[d0 + 1] = excl + v0;
+  }
+  __syncthreads();
+  TRACE(3)
+  // stage in CTA-sorted order (needs no global information: overlaps the look-back)
+#pragma unroll
+  for (int r = 0; r < ITEMS; r++) {
+    const uint32_t i = wstart + r * 32 + lane;
+    if (i < N) {
+      const uint32_t digit = (uint32_t)(key[r] >> shift) & mask;
+      s_stage[s_loc[digit] + my_cnt[digit] + rank[r]] = key[r];
+    }
+  }
+  TRACE(4)
+  // look back; s_base[d] becomes (global position of the CTA's first word of digit d) - s_loc[d]
+  for (int d = tid; d < bins; d += SORT_THREADS) {
+    const uint32_t total = s_base[d];
+    uint32_t excl = 0;
+    if (bid > 0) {
+      int p = (int)bid - 1;
+      while (true) {
+        uint32_t sv;
+        do {
+          sv = ld_volatile_u32(&status[(size_t)p * bins + d]);
+        } while ((sv >> 30) == 0u);
+        excl += sv & VAL_MASK;
+        if ((sv >> 30) == 2u) break;
+        p--;
+      }
+      st_volatile_u32(&my_status[d], FLAG_INCL | (excl + total));
+    }
+    s_base[d] = digit_base[d] + excl - s_loc[d];
+  }
+  TRACE(5)
+  __syncthreads();
+  TRACE(6)
+
+  const unsigned long long idx_mask = (1ull << idx_bits) - 1ull;
+  bool cull_on = false;
+  float inv_period = 0.0f;
+  if (mp.sub_mask) {
+    const float fx = mp.projmatrix[0], fy = mp.projmatrix[5], cy = mp.projmatrix[9];
+    inv_period = 1.0f / (6.2831853f * fabsf(fx));
+    // culling assumes |elevation| < pi/2 on every image row
+    cull_on = fmaxf(fabsf((0.0f - cy) / fy), fabsf(((float)(mp.H - 1) - cy) / fy)) < 1.55f;
+  }
+  // four words per thread and step, their cull boxes fetched together: the gathers are
+  // independent L2 round trips, not a chain
+  constexpr int WU = 4;
+  for (uint32_t j0 = tid; j0 < count; j0 += WU * SORT_THREADS) {
+    unsigned long long k[WU];
+    float4 cb[WU];
+#pragma unroll
+    for (int u = 0; u < WU; u++) {
+      const uint32_t j = j0 + u * SORT_THREADS;
+      k[u] = j < count ? s_stage[j] : 0ull;
+    }
+    if (cull_on) {
+#pragma unroll
+      for (int u = 0; u < WU; u++)
+        cb[u] = __ldg(&mp.cull[min((uint32_t)(k[u] & idx_mask), P - 1u)]);
+    }
+#pragma unroll
+    for (int u = 0; u < WU; u++) {
+      const uint32_t j = j0 + u * SORT_THREADS;
+      if (j >= count) continue;
+      const uint32_t digit = (uint32_t)(k[u] >> shift) & mask;
+      const uint32_t pos = j + s_base[digit];
+      if (pos >= capacity) continue;   // only when the capacity hint was too small
+      const uint32_t idx = (uint32_t)(k[u] & idx_mask);
+      const uint32_t d27 = (uint32_t)(k[u] >> idx_bits) & ((1u << SPLAT_DEPTH_BITS) - 1u);
+      const uint32_t tile = (uint32_t)(k[u] >> (idx_bits + SPLAT_DEPTH_BITS));
+      keys_out[pos] =
+          ((unsigned long long)tile << 32) | (unsigned long long)(d27 + SPLAT_DEPTH_BASE);
+      plist_out[pos] = idx;
+      if (mp.sub_mask) {
+        uint32_t sm = 0xffffu;
+        if (cull_on)
+          sm = subtile_mask(cb[u], (float)((tile % mp.tiles_x) * SPLAT_TILE),
+                            (float)((tile / mp.tiles_x) * SPLAT_TILE), inv_period);
+        mp.sub_mask[pos] = (uint16_t)sm;
+      }
+    }
+  }
+  TRACE(7)
+}
+
 }  // namespace
+
+#ifdef SORT_TRACE
+extern "C" __attribute__((visibility("default"))) int splat_debug_sort_trace(unsigned long long *out) {
+  return (int)cudaMemcpyFromSymbol(out, g_trace, sizeof(g_trace));
+}
+#endif
 
 void launch_digit_scan(const uint32_t *hist, uint32_t *digit_base, int npass, uint2 *ranges,
                        uint32_t *tile_order, int tiles, int tile_pass_single, int nrepl,
@@ -262,36 +453,87 @@ void launch_digit_scan(const uint32_t *hist, uint32_t *digit_base, int npass, ui
                                                     tile_pass_single, nrepl);
 }
 
+// Keys per thread of a pass: all CTAs of a pass are resident one per SM, so a pass runs in
+// ceil(#CTAs / #SMs) waves of (fixed cost + per-key cost * keys per thread).  215 CTAs of 16
+// keys per thread are two waves, the second a third full; 287 CTAs of 12 are two full, shorter
+// ones.  `n_estimate`: the expected number of words (the capacity may be a generous hint).
+static int pick_items(uint32_t n_estimate) {
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1)
+      sms = 148;
+  }
+  const int choices[3] = {16, 12, 8};
+  int best = 16;
+  long long best_cost = -1;
+  for (int c = 0; c < 3; c++) {
+    const long long ctas = ((long long)n_estimate + SORT_THREADS * choices[c] - 1) / (SORT_THREADS * choices[c]);
+    const long long waves = (ctas + sms - 1) / sms;
+    const long long cost = (waves < 1 ? 1 : waves) * (10 + choices[c]);   // fixed part ~ 10 keys
+    if (best_cost < 0 || cost < best_cost) {
+      best_cost = cost;
+      best = choices[c];
+    }
+  }
+  return best;
+}
+
+template <int ITEMS>
+static void launch_one_pass(bool last, const unsigned long long *src, unsigned long long *dst,
+                            unsigned long long *keys_out, uint32_t *plist_out,
+                            const MaskParams &mp, uint32_t P, const uint32_t *num_ptr,
+                            uint32_t capacity, uint32_t *status, uint32_t *ticket,
+                            const uint32_t *digit_base, int shift, int bits, int idx_bits,
+                            cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {   // the widest pass (10 bits) needs more than the default 48 KB
+    const int big = WARPS * SORT_MAX_BINS * 2 + SORT_MAX_BINS * 4;
+    cudaFuncSetAttribute(sort_pass_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
+    cudaFuncSetAttribute(sort_last_pass_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         big + SORT_MAX_BINS * 4 + SORT_THREADS * ITEMS * 8);
+    attr_set = true;
+  }
+  const int nbins = 1 << bits;
+  const int nblk = (int)(((size_t)capacity + SORT_THREADS * ITEMS - 1) / (SORT_THREADS * ITEMS));
+  const size_t smem = (size_t)WARPS * nbins * 2 + (size_t)nbins * 4;
+  if (nblk < 1) return;
+  if (last)
+    sort_last_pass_kernel<ITEMS><<<nblk, SORT_THREADS,
+                                   smem + (size_t)nbins * 4 + (size_t)SORT_THREADS * ITEMS * 8, s>>>(
+        src, keys_out, plist_out, mp, P, num_ptr, capacity, status, ticket, digit_base, shift, bits,
+        idx_bits);
+  else
+    sort_pass_kernel<ITEMS><<<nblk, SORT_THREADS, smem, s>>>(src, dst, num_ptr, capacity, status,
+                                                             ticket, digit_base, shift, bits);
+}
+
 // Runs `npass` passes ping-ponging between a and b (pass 0 reads a).  When
-// `unpack_last` the final pass writes keys_out / plist_out instead of a word array.
-// Returns the array that holds the sorted words otherwise.
+// `unpack_last` the final pass writes keys_out / plist_out (and mp->sub_mask) instead of a
+// word array.  Returns the array that holds the sorted words otherwise.  The status arrays
+// must hold SORT_MAX_BLOCKS(capacity) entries per digit (the layouts size them so).
 unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long *b,
                                        unsigned long long *keys_out, uint32_t *plist_out,
                                        const uint32_t *num_ptr, uint32_t capacity,
                                        uint32_t *status, const size_t *status_off,
                                        uint32_t *tickets, const uint32_t *digit_base,
                                        int npass, const int *shift, const int *bits,
-                                       int unpack_last, int idx_bits, int nblk,
-                                       cudaStream_t s) {
+                                       int unpack_last, int idx_bits, uint32_t n_estimate,
+                                       cudaStream_t s, const MaskParams *mp, uint32_t P) {
   unsigned long long *src = a, *dst = b;
-  static bool attr_set = false;
-  if (!attr_set) {   // the widest pass (10 bits) needs more than the default 48 KB
-    const int big = WARPS * SORT_MAX_BINS * 2 + SORT_MAX_BINS * 4;
-    cudaFuncSetAttribute(sort_pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
-    cudaFuncSetAttribute(sort_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
-    attr_set = true;
-  }
+  const int items = pick_items(n_estimate ? n_estimate : capacity);
+  const MaskParams none{};
   for (int p = 0; p < npass; p++) {
-    const int nbins = 1 << bits[p];
-    const size_t smem = (size_t)WARPS * nbins * 2 + (size_t)nbins * 4;
-    if (unpack_last && p == npass - 1)
-      sort_pass_kernel<true><<<nblk, SORT_THREADS, smem, s>>>(
-          src, dst, keys_out, plist_out, num_ptr, capacity, status + status_off[p], tickets + p,
-          digit_base + p * SORT_MAX_BINS, shift[p], bits[p], idx_bits);
-    else
-      sort_pass_kernel<false><<<nblk, SORT_THREADS, smem, s>>>(
-          src, dst, keys_out, plist_out, num_ptr, capacity, status + status_off[p], tickets + p,
-          digit_base + p * SORT_MAX_BINS, shift[p], bits[p], idx_bits);
+    const bool last = unpack_last && p == npass - 1;
+#define ONE_PASS(I)                                                                             \
+  launch_one_pass<I>(last, src, dst, keys_out, plist_out, mp ? *mp : none, P, num_ptr, capacity, \
+                     status + status_off[p], tickets + p, digit_base + p * SORT_MAX_BINS,        \
+                     shift[p], bits[p], idx_bits, s)
+    if (items == 16) ONE_PASS(16);
+    else if (items == 12) ONE_PASS(12);
+    else ONE_PASS(8);
+#undef ONE_PASS
     unsigned long long *t = dst;
     dst = src;
     src = t;
@@ -300,7 +542,7 @@ unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long
 }
 
 void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, const BinView &b,
-                 const SortPlan &sp, uint32_t capacity, cudaStream_t s) {
+                 const SortPlan &sp, uint32_t capacity, uint32_t n_estimate, cudaStream_t s) {
   MaskParams mp;
   mp.sub_mask = b.sub_mask;
   mp.cull = g.cull;
@@ -312,7 +554,7 @@ void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, con
                     HIST_REPL, s);
   launch_sort_passes(b.words_a, b.words_b, b.keys, b.point_list, &g.hdr->num_rendered,
                      capacity, b.status, b.status_off, b.tickets, b.digit_base, sp.npass,
-                     sp.shift, sp.bits, 1, sp.idx_bits, b.nblk, s);
+                     sp.shift, sp.bits, 1, sp.idx_bits, n_estimate, s, &mp, (uint32_t)p.P);
   if (single < 0) {
     cudaMemsetAsync(im.ranges, 0, (size_t)im.tiles * sizeof(uint2), s);
     uint32_t blocks = (capacity + 255) / 256;
@@ -322,7 +564,4 @@ void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, con
   }
   if (single < 0 && im.tiles <= SPLAT_MAX_ORDERED_TILES)   // beyond that: identity order
     tile_order_kernel<<<(im.tiles + 127) / 128, 128, 0, s>>>(im.ranges, im.tiles, im.tile_order);
-  if (capacity)
-    sub_mask_kernel<<<(capacity + 255) / 256, 256, 0, s>>>(&g.hdr->num_rendered, capacity, b.keys,
-                                                           b.point_list, mp, (uint32_t)p.P);
 }

@@ -57,7 +57,7 @@ struct KnnLayout {
   uint32_t cnt[MAXL];
   size_t box_off[MAXL];  // in nodes
   __host__ explicit KnnLayout(int P) {
-    nblk = (P + SORT_BLOCK_ELEMS - 1) / SORT_BLOCK_ELEMS;
+    nblk = (P + SORT_MIN_BLOCK_ELEMS - 1) / SORT_MIN_BLOCK_ELEMS;
     if (nblk < 1) nblk = 1;
     nlevel = 0;
     uint32_t c = (uint32_t)((P + LEAF - 1) / LEAF);
@@ -338,7 +338,7 @@ int sknn_dist2(int P, const float *points, float *mean_dists, void *workspace,
   launch_digit_scan(hist, digit_base, plan.npass, nullptr, nullptr, 0, -1, HIST_REPL, st);
   unsigned long long *res = launch_sort_passes(wa, wb, nullptr, nullptr, num, (uint32_t)P, status,
                                                L.status_off, tickets, digit_base, plan.npass,
-                                               plan.shift, plan.bits, 0, plan.idx_bits, L.nblk, st);
+                                               plan.shift, plan.bits, 0, plan.idx_bits, (uint32_t)P, st);
   const int leaves = (P + LEAF - 1) / LEAF;
   gather_leaf_kernel<<<(leaves * LEAF + 255) / 256, 256, 0, st>>>(P, points, res, plan.idx_bits,
                                                                   sorted, boxes);
