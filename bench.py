@@ -7,7 +7,8 @@ A "step" is one pass of the hot path over one synthetic frame: rasterizer forwar
 backward through the reference-facing `_C` calls (which go through the C-ABI of
 libsplat_b200.so).  N=1 runs BASELINE config C2 (64x1024 image, 500k surfels).  N>1 is the
 keyframe-sharded window (weak scaling): every rank renders its own keyframe of the same
-surfel set and the per-surfel [P,10] gradient buffers are all-reduced with NCCL.
+surfel set and the per-surfel [P,10] gradient buffers are summed over NVLink peer memory
+(push fused into the VJP kernel; SPLAT_B200_XCHG=nccl selects one NCCL all-reduce instead).
 
 Rank 0 prints ONE JSON line.  See DESIGN.md "Measurement" for every field.
 """
@@ -350,8 +351,9 @@ def run_ours(args, rank, world, local_rank):
                    "parallelism": f"keyframe-sharded x{world}"},
         "e2e": {"value": world * 1e3 / (e2e_ms / args.steps), "unit": UNIT,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-        # 10 forward + 2 backward kernels per frame (+ reduce and wait of the exchange)
-        "gpu_launches": (14 if xchg else 12) * args.steps,
+        # 9 forward (preprocess, chunk scan, emit, digit scan, 4 sort passes, render) + 2
+        # backward kernels per frame (+ the exchange's reduce kernel)
+        "gpu_launches": (12 if xchg else 11) * args.steps,
         "stage_ms": stage_ms,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak,
                      "peak_source": peak_src, "unit": "GB/s",
