@@ -68,7 +68,7 @@ struct GeomLayout {
 };
 
 struct ImageLayout {
-  size_t final_T, n_contrib, ranges, tile_order, total;
+  size_t final_T, n_contrib, ranges, tile_order, sub_cost, bwd_order, total;
   int tiles_x, tiles_y, tiles;
   __host__ ImageLayout(int W, int H) {
     tiles_x = (W + SPLAT_TILE - 1) / SPLAT_TILE;
@@ -80,6 +80,8 @@ struct ImageLayout {
     n_contrib = o; o = align_up(o + HW * 8, 256);
     ranges = o;    o = align_up(o + (size_t)tiles * 8, 256);
     tile_order = o; o = align_up(o + (size_t)tiles * 4, 256);
+    sub_cost = o;  o = align_up(o + (size_t)tiles * 16 * 4, 256);   // per 4x4 sub-tile
+    bwd_order = o; o = align_up(o + (size_t)tiles * 16 * 4, 256);
     total = o + 256;
   }
 };
@@ -184,6 +186,8 @@ struct ImageView {
   uint32_t *n_contrib;
   uint2 *ranges;
   uint32_t *tile_order;   // tiles sorted by decreasing list length (work scheduling)
+  uint32_t *sub_cost;     // per sub-tile (tile * 16 + sub): list entries the forward consumed
+  uint32_t *bwd_order;    // sub-tiles by decreasing sub_cost: the backward's CTA numbering
   int tiles_x, tiles_y, tiles;
 };
 struct BinView {
@@ -222,6 +226,8 @@ static inline ImageView make_image_view(const char *buf, int W, int H) {
   v.n_contrib = (uint32_t *)(b + L.n_contrib);
   v.ranges = (uint2 *)(b + L.ranges);
   v.tile_order = (uint32_t *)(b + L.tile_order);
+  v.sub_cost = (uint32_t *)(b + L.sub_cost);
+  v.bwd_order = (uint32_t *)(b + L.bwd_order);
   v.tiles_x = L.tiles_x;
   v.tiles_y = L.tiles_y;
   v.tiles = L.tiles;
@@ -290,6 +296,7 @@ unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long
                                        int unpack_last, int idx_bits, uint32_t n_estimate,
                                        cudaStream_t s, const MaskParams *mp = nullptr,
                                        uint32_t P = 0);
+void launch_bwd_order(const ImageView &im, cudaStream_t s);
 void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageView &im,
                            const BinView &b, uint32_t capacity, cudaStream_t s);
 

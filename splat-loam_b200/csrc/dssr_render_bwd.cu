@@ -71,7 +71,7 @@ __device__ __forceinline__ StepOut recur(BackState &b, const PixelConst &c, floa
 // traversal machinery as the forward (sub-tile masks, double-buffered staging), walked back
 // to front; lanes 0-15 handle the later surfel of a pair, lanes 16-31 the earlier one.
 __global__ void __launch_bounds__(32)
-render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restrict__ tile_order,
+render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restrict__ bwd_order,
                        const uint32_t *__restrict__ point_list,
                        const uint16_t *__restrict__ sub_mask_base, const BinHeader *__restrict__ bhdr,
                        const float4 *__restrict__ rec, const float *__restrict__ projmatrix, int W,
@@ -85,8 +85,9 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
   __shared__ uint32_t s_id[2][32];
   const int lane = threadIdx.x, half = lane >> 4, p16 = lane & 15;
   const uint32_t work = blockIdx.x;
-  const uint32_t tile = tile_order ? tile_order[work / SUBS_PER_TILE] : work / SUBS_PER_TILE;
-  const int sub = work % SUBS_PER_TILE;
+  const uint32_t unit = bwd_order[work];          // sub-tiles by decreasing walk length
+  const uint32_t tile = unit / SUBS_PER_TILE;
+  const int sub = unit % SUBS_PER_TILE;
   const int x0 = (tile % tiles_x) * SPLAT_TILE + (sub & 3) * SUB;
   const int y0 = (tile / tiles_x) * SPLAT_TILE + (sub >> 2) * SUB;
   if (x0 >= W || y0 >= H) return;
@@ -429,10 +430,9 @@ backward_preprocess_kernel(int P, const int *__restrict__ radii,
 
 void launch_render_backward(const BwdParams &p, const GeomView &g, const ImageView &im,
                             const BinView &b, cudaStream_t s) {
-  const uint32_t *order = im.tiles <= SPLAT_MAX_ORDERED_TILES ? im.tile_order : nullptr;
   render_backward_kernel<<<im.tiles * SUBS_PER_TILE, 32, 0, s>>>(
-      im.ranges, order, b.point_list, reinterpret_cast<const uint16_t *>(b.hdr), b.hdr, g.rec, p.projmatrix, p.W, p.H, im.tiles_x, (uint32_t)p.P, im.final_T, im.n_contrib,
-      p.dL_dout, p.dL_dtransMat, p.dL_dnormal, p.dL_dopacity);
+      im.ranges, im.bwd_order, b.point_list, reinterpret_cast<const uint16_t *>(b.hdr), b.hdr, g.rec,
+      p.projmatrix, p.W, p.H, im.tiles_x, (uint32_t)p.P, im.final_T, im.n_contrib, p.dL_dout, p.dL_dtransMat, p.dL_dnormal, p.dL_dopacity);
 }
 
 void launch_backward_preprocess(const BwdParams &p, cudaStream_t s) {
