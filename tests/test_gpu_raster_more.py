@@ -1,0 +1,138 @@
+"""GPU: further parity cases of the rasterizer against the unmodified reference CUDA build
+(oracle/_ref) and behavioural checks of the C-ABI (streams, host threads, prefiltered)."""
+import threading
+
+import numpy as np
+import pytest
+import torch
+
+import scenes
+from conftest import assert_n_contrib_equal, cosine, rel_l2
+from gpu_helpers import bits, run_product, to_cuda
+
+pytestmark = pytest.mark.gpu
+GRADS = ("means3D", "opacity", "scales", "rotations", "transMat")
+
+
+def _reference(s, scale_modifier=1.0, backward=True):
+    import reflib
+    if not reflib.available():
+        pytest.skip("oracle/_ref/libref_splat.so not built")
+    c = to_cuda(s)
+    ref = reflib.RefRasterizer()
+    R, out, radii = ref.forward(c["means3D"], c["opacities"].reshape(-1), c["scales"], c["rotations"],
+                                c["viewmatrix"], c["projmatrix"], s["H"], s["W"],
+                                scale_modifier=scale_modifier)
+    g = {"num_rendered": R, "out": out.cpu().numpy(), "radii": radii.cpu().numpy()}
+    for nm in ("keys", "point_list", "ranges", "n_contrib"):
+        g[nm] = ref.state(nm).numpy()
+    if backward:
+        for k, v in ref.backward(c["dL_dout"], scale_modifier=scale_modifier).items():
+            g["grad_" + k] = v.cpu().numpy()
+    return g
+
+
+def _product(s, scale_modifier=1.0):
+    from diff_surfel_spherical_rasterization import _C
+    c = to_cuda(s)
+    empty = torch.empty(0, device="cuda")
+    R, out, radii, geom, binning, img = _C.rasterize_gaussians(
+        c["means3D"], c["opacities"], c["scales"], c["rotations"], scale_modifier, empty,
+        c["viewmatrix"], c["projmatrix"], s["H"], s["W"], False, False)
+    r = {"num_rendered": R, "out": out.cpu().numpy(), "radii": radii.cpu().numpy()}
+    for nm in ("keys", "point_list", "ranges", "n_contrib"):
+        r[nm] = _C.debug_state(geom, binning, img, nm).numpy()
+    g = _C.rasterize_gaussians_backward(c["means3D"], radii, c["scales"], c["rotations"],
+                                        scale_modifier, empty, c["viewmatrix"], c["projmatrix"],
+                                        c["dL_dout"], geom, R, binning, img, False)
+    for nm, t in zip(("means2D", "opacity", "means3D", "transMat", "scales", "rotations"), g):
+        r["grad_" + nm] = t.cpu().numpy()
+    return r
+
+
+def _compare(r, g, HW):
+    assert r["num_rendered"] == g["num_rendered"]
+    assert np.array_equal(r["radii"], g["radii"])
+    for nm in ("keys", "point_list", "ranges"):
+        a, b = (np.ascontiguousarray(x).ravel().view(np.uint8) for x in (r[nm], g[nm]))
+        assert np.array_equal(a, b), nm
+    assert np.array_equal(bits(r["out"]), bits(g["out"]))
+    assert_n_contrib_equal(r["n_contrib"], g["n_contrib"], HW)
+    for k in GRADS:
+        if "grad_" + k in g:
+            assert rel_l2(r["grad_" + k], g["grad_" + k]) < 1e-4, k
+            assert cosine(r["grad_" + k], g["grad_" + k]) > 0.9999, k
+
+
+@pytest.mark.parametrize("scale_modifier", [0.6, 1.7])
+def test_scale_modifier_matches_reference(native_lib, scale_modifier):
+    """The forward scales the surfels (forward.cu:122-126); the backward does not apply the
+    modifier to dL_dscales (quirk Q5) - both as the reference."""
+    s = scenes.make_scene("C1")
+    _compare(_product(s, scale_modifier), _reference(s, scale_modifier), s["H"] * s["W"])
+
+
+def test_two_tile_digit_passes_match_reference(native_lib):
+    """128x2048 pixels = 1024 tiles is the last single-pass size; 144x2064 needs 11 tile bits,
+    i.e. two tile passes, identifyTileRanges and the tile_order kernel."""
+    s = scenes.make_scene((144, 2064, 45.0, 60000))
+    r, g = _product(s), _reference(s)
+    assert ((s["H"] + 15) // 16) * ((s["W"] + 15) // 16) > 1024
+    _compare(r, g, s["H"] * s["W"])
+
+
+def test_non_default_stream_and_interleaving(native_lib):
+    """Everything is enqueued on the caller's current stream: two frames on two streams give
+    the results of the same frames run alone."""
+    frames = [scenes.make_scene("C0", keyframe=k) for k in range(2)]
+    alone = [run_product(f, state=()) for f in frames]
+    streams = [torch.cuda.Stream() for _ in frames]
+    res = [None, None]
+    for rep in range(3):
+        for i, (f, st) in enumerate(zip(frames, streams)):
+            with torch.cuda.stream(st):
+                res[i] = run_product(f, state=())
+    for a, b in zip(alone, res):
+        assert np.array_equal(bits(a["out"]), bits(b["out"]))
+        for k in GRADS:
+            assert rel_l2(b["grad_" + k], a["grad_" + k]) < 1e-5, k
+
+
+def test_two_host_threads(native_lib):
+    """Per-thread host state (pinned count word, event, last error): two threads render
+    different frames concurrently on their own streams."""
+    frames = [scenes.make_scene("C0", keyframe=k) for k in range(2)]
+    alone = [run_product(f, state=()) for f in frames]
+    out, err = [None, None], []
+
+    def work(i):
+        try:
+            torch.cuda.set_device(0)
+            with torch.cuda.stream(torch.cuda.Stream()):
+                for _ in range(5):
+                    out[i] = run_product(frames[i], state=())
+        except Exception as e:   # pragma: no cover
+            err.append(e)
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not err, err
+    for a, b in zip(alone, out):
+        assert np.array_equal(bits(a["out"]), bits(b["out"]))
+
+
+def test_prefiltered_with_a_culled_surfel_is_an_error(native_lib):
+    """The reference __trap()s the device (forward.cu:131-137); here it is a RuntimeError with
+    the reference's message and the process lives on."""
+    from diff_surfel_spherical_rasterization import _C
+    s = scenes.make_scene("C0")
+    c = to_cuda(s)
+    c["means3D"] = c["means3D"].clone()
+    c["means3D"][0] = torch.tensor([1e4, 0.0, 0.0], device="cuda")     # beyond the 120 m range
+    empty = torch.empty(0, device="cuda")
+    with pytest.raises(RuntimeError, match="filtered although prefiltered"):
+        _C.rasterize_gaussians(c["means3D"], c["opacities"], c["scales"], c["rotations"], 1.0, empty,
+                               c["viewmatrix"], c["projmatrix"], s["H"], s["W"], True, False)
+    r = run_product(s, state=())      # and the next frame is fine
+    assert np.isfinite(r["out"]).all()
