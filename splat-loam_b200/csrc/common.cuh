@@ -296,6 +296,16 @@ unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long
                                        int unpack_last, int idx_bits, uint32_t n_estimate,
                                        cudaStream_t s, const MaskParams *mp = nullptr,
                                        uint32_t P = 0);
+// Function attributes (opt-in shared memory, carve-out) are per device: true the first time a
+// call site runs on the current device (one bit per device in the caller's static mask).
+static inline bool first_use_on_device(unsigned long long &seen) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (seen & bit) return false;
+  seen |= bit;
+  return true;
+}
 void launch_bwd_order(const ImageView &im, cudaStream_t s);
 void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageView &im,
                            const BinView &b, uint32_t capacity, cudaStream_t s);

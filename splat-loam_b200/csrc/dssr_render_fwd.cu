@@ -295,12 +295,10 @@ void launch_bwd_order(const ImageView &im, cudaStream_t s) {
 void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageView &im,
                            const BinView &b, uint32_t capacity, cudaStream_t s) {
   const uint32_t *order = im.tiles <= SPLAT_MAX_ORDERED_TILES ? im.tile_order : nullptr;
-  static bool carveout_set = false;
-  if (!carveout_set) {   // one-warp CTAs: residency is limited by the shared-memory carve-out
+  static unsigned long long seen = 0;
+  if (first_use_on_device(seen))   // one-warp CTAs: residency is limited by the carve-out
     cudaFuncSetAttribute(render_forward_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                          cudaSharedmemCarveoutMaxShared);
-    carveout_set = true;
-  }
   render_forward_kernel<<<im.tiles * SUBS_PER_TILE, 32, 0, s>>>(
       im.ranges, order, b.point_list, b.sub_mask, g.rec, p.projmatrix, p.W, p.H, im.tiles_x,
       capacity, (uint32_t)p.P, im.final_T, im.n_contrib, p.out_maps, im.sub_cost);

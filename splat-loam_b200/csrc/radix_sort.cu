@@ -487,13 +487,12 @@ static void launch_one_pass(bool last, const unsigned long long *src, unsigned l
                             uint32_t capacity, uint32_t *status, uint32_t *ticket,
                             const uint32_t *digit_base, int shift, int bits, int idx_bits,
                             cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {   // the widest pass (10 bits) needs more than the default 48 KB
+  static unsigned long long seen = 0;
+  if (first_use_on_device(seen)) {   // the widest pass (10 bits) needs more than the default 48 KB
     const int big = WARPS * SORT_MAX_BINS * 2 + SORT_MAX_BINS * 4;
     cudaFuncSetAttribute(sort_pass_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
     cudaFuncSetAttribute(sort_last_pass_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          big + SORT_MAX_BINS * 4 + SORT_THREADS * ITEMS * 8);
-    attr_set = true;
   }
   const int nbins = 1 << bits;
   const int nblk = (int)(((size_t)capacity + SORT_THREADS * ITEMS - 1) / (SORT_THREADS * ITEMS));
