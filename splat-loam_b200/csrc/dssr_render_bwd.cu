@@ -17,6 +17,18 @@
 #include "peer_exchange.cuh"
 #include "raster_math.cuh"
 
+#ifdef RENDER_TRACE
+__device__ unsigned long long g_btrace[8192][4];
+extern "C" __attribute__((visibility("default"))) int splat_debug_bwd_trace(unsigned long long *out) {
+  return (int)cudaMemcpyFromSymbol(out, g_btrace, sizeof(g_btrace));
+}
+__device__ __forceinline__ unsigned long long btime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#endif
+
 namespace {
 
 constexpr int SUB = 4;                                            // 4x4 pixels per warp
@@ -85,6 +97,12 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
   __shared__ uint32_t s_id[2][32];
   const int lane = threadIdx.x, half = lane >> 4, p16 = lane & 15;
   const uint32_t work = blockIdx.x;
+#ifdef RENDER_TRACE
+  if (lane == 0 && work < 8192) {   // written at once: nothing extra stays live in registers
+    g_btrace[work][0] = btime();
+    g_btrace[work][1] = 0;
+  }
+#endif
   const uint32_t unit = bwd_order[work];          // sub-tiles by decreasing walk length
   const uint32_t tile = unit / SUBS_PER_TILE;
   const int sub = unit % SUBS_PER_TILE;
@@ -102,6 +120,9 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
 #pragma unroll
   for (int o = 8; o > 0; o >>= 1)
     max_last = max(max_last, __shfl_xor_sync(0xffffffffu, max_last, o));
+#ifdef RENDER_TRACE
+  if (lane == 0 && work < 8192) g_btrace[work][2] = max_last;
+#endif
   if (max_last == 0) return;
   // the forward stored the offset of the mask array in the buffer's header (the capacity it
   // was laid out with is not known to the backward's caller)
@@ -312,6 +333,9 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
     m = nm;
     __syncwarp();
   }
+#ifdef RENDER_TRACE
+  if (lane == 0 && blockIdx.x < 8192) g_btrace[blockIdx.x][1] = btime();
+#endif
 }
 
 // Per-surfel VJP: dL/dT, dL/dnormal -> dL/dmean3D, dL/dscale, dL/dquat.

@@ -20,7 +20,7 @@ torch.cuda.synchronize()
 buf = np.zeros((8192, 4), dtype=np.uint64)
 assert n.load().splat_debug_bwd_trace(buf.ctypes.data_as(ctypes.c_void_p)) == 0
 t = buf.astype(np.int64)
-t = t[t[:, 0] > 0]
+t = t[(t[:, 0] > 0) & (t[:, 1] > 0)]
 t0 = t[:, 0].min()
 start, end = (t[:, 0] - t0) / 1e3, (t[:, 1] - t0) / 1e3
 dur, cost = end - start, t[:, 2]
@@ -29,8 +29,8 @@ print(f"{len(t)} warps; kernel span {span:.1f} us; sum of warp time {dur.sum() /
       f"{dur.sum() / span / 148:.1f} warps busy per SM on average")
 print("warp duration us: median %.1f  p90 %.1f  p99 %.1f  max %.1f" % tuple(np.percentile(dur, [50, 90, 99, 100])))
 print("start time us:    median %.1f  p75 %.1f p90 %.1f  max %.1f" % tuple(np.percentile(start, [50, 75, 90, 100])))
-print("corr(duration, traversed entries) = %.3f ; corr(duration, list length) = %.3f" %
-      (np.corrcoef(dur, cost)[0, 1], np.corrcoef(dur, t[:, 3])[0, 1]))
+print("corr(duration, traversed entries) = %.3f" % np.corrcoef(dur, cost)[0, 1])
+print("us per traversed entry: %.4f" % (dur.sum() / max(cost.sum(), 1)))
 for q in range(100, int(span) + 100, 100):
     print(f"  running at {q} us: {((start <= q) & (end > q)).sum()}", end=";")
 print()
