@@ -330,9 +330,11 @@ def run_ours(args, rank, world, local_rank):
     ab = algorithmic_bytes(P, R, Nc, H * W)
     peak, peak_src = measured_peak_gbs()
     stage_ms[dom] = dom_ms or stage_ms.get(dom)
-    traffic = None
+    traffic = winst = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dom)
+        prof = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        traffic = prof.get(dom)
+        winst = prof.get("warp_instructions", {}).get(dom) if args.config == "C2" else None
     except Exception:
         pass
     achieved = ab[dom] / (stage_ms[dom] * 1e-3) / 1e9 if stage_ms.get(dom) else None
@@ -364,6 +366,14 @@ def run_ours(args, rank, world, local_rank):
                            "frac": ab["frame"] / (ms_per_step * 1e-3) / 1e9 / peak},
         "clocks": clocks,
     }
+    if winst and stage_ms.get(dom) and clocks and clocks.get("sm_mhz"):
+        # the compositing kernels are bound by instruction issue, not by HBM: warp instructions
+        # per launch (ncu, profiles/) / live launch duration, against 4 issue slots per SM and clock
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        ipeak = sms * 4 * clocks["sm_mhz"] * 1e6
+        line["issue_roofline"] = {"kernel": dom, "warp_instructions": winst,
+                                  "achieved": winst / (stage_ms[dom] * 1e-3), "peak": ipeak,
+                                  "unit": "warp-inst/s", "frac": winst / (stage_ms[dom] * 1e-3) / ipeak}
     if world == 1:
         line["post"] = post_stage(allmap.detach(), t)
         line["optimizer"] = adam_stage(P, dev)
