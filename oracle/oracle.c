@@ -522,7 +522,10 @@ void orc_subtile_stats(int W, int H, const uint32_t *ranges, const uint32_t *poi
     for (uint32_t e = 0; e < trav; e++) {
       uint32_t id = point_list[r0 + e];
       const float *b = boxes + 4 * (size_t)id;
-      if (b[2] > sy + 3 || b[3] < sy || b[0] > sx + 3 || b[1] < sx) continue;
+      /* x is periodic with the azimuth period 2*pi*|fx| (as raster_math.cuh:cull_overlap) */
+      const double ip = 1.0 / (6.283185307179586 * fabs((double)proj[0]));
+      if (b[2] > sy + 3 || b[3] < sy ||
+          floor(((double)(sx + 3) - b[0]) * ip) < ceil(((double)sx - b[1]) * ip)) continue;
       nb++;
       int any = 0;
       for (int l = 0; l < 16 && !any; l++) {
