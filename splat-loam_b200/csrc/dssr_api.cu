@@ -290,10 +290,23 @@ int dssr_backward(const dssr_backward_args *a) {
     return fail("dssr_backward: scales / dL_dscales must be 8-byte and rotations / "
                 "dL_drotations / dL_dtransMat 16-byte aligned");
   const bool dbg = a->debug & 1;
-  CUDA_TRY(cudaMemsetAsync(a->dL_dmeans2D, 0, 12 * P, st));
-  CUDA_TRY(cudaMemsetAsync(a->dL_dnormal, 0, 12 * P, st));
-  CUDA_TRY(cudaMemsetAsync(a->dL_dopacity, 0, 4 * P, st));
-  CUDA_TRY(cudaMemsetAsync(a->dL_dtransMat, 0, 48 * P, st));
+  {
+    // the four accumulation targets must start at zero; when the caller laid them out back to
+    // back (as _C.py does, one allocation) that is ONE fill instead of four
+    char *ptr[4] = {(char *)a->dL_dmeans2D, (char *)a->dL_dnormal, (char *)a->dL_dopacity,
+                    (char *)a->dL_dtransMat};
+    const size_t len[4] = {12 * P, 12 * P, 4 * P, 48 * P};
+    char *lo = ptr[0], *hi = ptr[0] + len[0];
+    for (int i = 1; i < 4; i++) {
+      if (ptr[i] < lo) lo = ptr[i];
+      if (ptr[i] + len[i] > hi) hi = ptr[i] + len[i];
+    }
+    if ((size_t)(hi - lo) <= 76 * P + 4096) {
+      CUDA_TRY(cudaMemsetAsync(lo, 0, (size_t)(hi - lo), st));
+    } else {
+      for (int i = 0; i < 4; i++) CUDA_TRY(cudaMemsetAsync(ptr[i], 0, len[i], st));
+    }
+  }
   ImageLayout il(a->W, a->H);
   SortPlan sp(a->P, il.tiles);
   GeomView gv = make_geom_view(a->geom_buffer, a->P);
