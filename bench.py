@@ -353,8 +353,8 @@ def run_ours(args, rank, world, local_rank):
                    "parallelism": f"keyframe-sharded x{world}"},
         "e2e": {"value": world * 1e3 / (e2e_ms / args.steps), "unit": UNIT,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-        # 10 forward (preprocess, chunk scan, emit, digit scan, 4 sort passes, render, backward
-        # work order) + 2 backward kernels per frame (+ the exchange's reduce kernel)
+        # 9 forward (preprocess, chunk scan, emit, digit scan, 4 sort passes, render) + 3 backward
+        # kernels (work order, render, per-surfel VJP) per frame (+ the exchange's reduce kernel)
         "gpu_launches": (13 if xchg else 12) * args.steps,
         "stage_ms": stage_ms,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak,

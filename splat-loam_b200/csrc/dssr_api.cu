@@ -331,6 +331,7 @@ int dssr_backward(const dssr_backward_args *a) {
   }
   {
     ProfScope ps("render_backward", st);
+    launch_bwd_order(iv, st);   // here, not in the forward: forward-only renders do not pay for it
     launch_render_backward(bp, gv, iv, bv, st);
   }
   LAUNCH_CHECK(dbg, st, "render_backward");

@@ -302,5 +302,4 @@ void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageVie
   render_forward_kernel<<<im.tiles * SUBS_PER_TILE, 32, 0, s>>>(
       im.ranges, order, b.point_list, b.sub_mask, g.rec, p.projmatrix, p.W, p.H, im.tiles_x,
       capacity, (uint32_t)p.P, im.final_T, im.n_contrib, p.out_maps, im.sub_cost);
-  launch_bwd_order(im, s);
 }
