@@ -501,8 +501,9 @@ void orc_pair_stats(int W, int H, const uint32_t *ranges, const uint32_t *point_
   stats[0] = s0; stats[1] = s1; stats[2] = s2; stats[3] = s3;
 }
 
-/* Developer statistics per 4x4 sub-tile: out[st*3+0..2] = traversed entries, entries whose
- * box overlaps the sub-tile, entries with at least one passing pixel. */
+/* Developer statistics per 4x4 sub-tile: out[st*5+0..4] = traversed entries, entries whose
+ * box overlaps the sub-tile, entries with at least one passing pixel, sum over the 32-entry
+ * steps of ceil(visited in step / 2) (the two-at-a-time evaluation steps), steps with a visit. */
 void orc_subtile_stats(int W, int H, const uint32_t *ranges, const uint32_t *point_list,
                        const float *xy, const float *T, const float *nrm_opa, const float *proj,
                        const uint32_t *n_contrib, const float *boxes, uint32_t *out) {
@@ -512,7 +513,7 @@ void orc_subtile_stats(int W, int H, const uint32_t *ranges, const uint32_t *poi
   for (int st = 0; st < nsx * nsy; st++) {
     int sx = (st % nsx) * 4, sy = (st / nsx) * 4;
     int tile = (sy / TILE) * gx + sx / TILE;
-    uint32_t r0 = ranges[2 * tile], trav = 0, nb = 0, nt = 0;
+    uint32_t r0 = ranges[2 * tile], trav = 0, nb = 0, nt = 0, in_step = 0, pairs = 0, busy = 0;
     ray_t rays[16];
     for (int l = 0; l < 16; l++) {
       int px = sx + (l & 3), py = sy + (l >> 2);
@@ -520,6 +521,7 @@ void orc_subtile_stats(int W, int H, const uint32_t *ranges, const uint32_t *poi
       if (px < W && py < H && n_contrib[(size_t)py * W + px] > trav) trav = n_contrib[(size_t)py * W + px];
     }
     for (uint32_t e = 0; e < trav; e++) {
+      if ((e & 31u) == 0u) { pairs += (in_step + 1) / 2; busy += in_step > 0; in_step = 0; }
       uint32_t id = point_list[r0 + e];
       const float *b = boxes + 4 * (size_t)id;
       /* x is periodic with the azimuth period 2*pi*|fx| (as raster_math.cuh:cull_overlap) */
@@ -527,6 +529,7 @@ void orc_subtile_stats(int W, int H, const uint32_t *ranges, const uint32_t *poi
       if (b[2] > sy + 3 || b[3] < sy ||
           floor(((double)(sx + 3) - b[0]) * ip) < ceil(((double)sx - b[1]) * ip)) continue;
       nb++;
+      in_step++;
       int any = 0;
       for (int l = 0; l < 16 && !any; l++) {
         int px = sx + (l & 3), py = sy + (l >> 2);
@@ -536,6 +539,7 @@ void orc_subtile_stats(int W, int H, const uint32_t *ranges, const uint32_t *poi
       }
       nt += any;
     }
-    out[3 * st] = trav; out[3 * st + 1] = nb; out[3 * st + 2] = nt;
+    pairs += (in_step + 1) / 2; busy += in_step > 0;
+    out[5 * st] = trav; out[5 * st + 1] = nb; out[5 * st + 2] = nt; out[5 * st + 3] = pairs; out[5 * st + 4] = busy;
   }
 }
