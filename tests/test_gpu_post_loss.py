@@ -37,7 +37,7 @@ def oracle64(g, which=3):
     losses = rp.mapper_image_losses(pkg, t("gt_depth"), torch.from_numpy(g["gt_valid"]),
                                     float(g["lambda_normal"]), float(g["lambda_alpha"]))
     losses[which].backward()
-    return [float(x) for x in losses], a.grad.numpy()
+    return [float(x.detach()) for x in losses], a.grad.numpy()
 
 
 @pytest.mark.parametrize("name", ("post_loss_c0", "post_loss_synth"))
