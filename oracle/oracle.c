@@ -501,9 +501,10 @@ void orc_pair_stats(int W, int H, const uint32_t *ranges, const uint32_t *point_
   stats[0] = s0; stats[1] = s1; stats[2] = s2; stats[3] = s3;
 }
 
-/* Developer statistics per 4x4 sub-tile: out[st*5+0..4] = traversed entries, entries whose
+/* Developer statistics per 4x4 sub-tile: out[st*7+0..6] = traversed entries, entries whose
  * box overlaps the sub-tile, entries with at least one passing pixel, sum over the 32-entry
- * steps of ceil(visited in step / 2) (the two-at-a-time evaluation steps), steps with a visit. */
+ * steps of ceil(visited in step / 2) (the two-at-a-time evaluation steps), steps with a visit, (pixel, visited
+ * entry) pairs whose pixel lies inside the entry's box, pairs that pass the alpha test. */
 void orc_subtile_stats(int W, int H, const uint32_t *ranges, const uint32_t *point_list,
                        const float *xy, const float *T, const float *nrm_opa, const float *proj,
                        const uint32_t *n_contrib, const float *boxes, uint32_t *out) {
@@ -513,7 +514,7 @@ void orc_subtile_stats(int W, int H, const uint32_t *ranges, const uint32_t *poi
   for (int st = 0; st < nsx * nsy; st++) {
     int sx = (st % nsx) * 4, sy = (st / nsx) * 4;
     int tile = (sy / TILE) * gx + sx / TILE;
-    uint32_t r0 = ranges[2 * tile], trav = 0, nb = 0, nt = 0, in_step = 0, pairs = 0, busy = 0;
+    uint32_t r0 = ranges[2 * tile], trav = 0, nb = 0, nt = 0, in_step = 0, pairs = 0, busy = 0, inbox = 0, okpix = 0;
     ray_t rays[16];
     for (int l = 0; l < 16; l++) {
       int px = sx + (l & 3), py = sy + (l >> 2);
@@ -531,15 +532,21 @@ void orc_subtile_stats(int W, int H, const uint32_t *ranges, const uint32_t *poi
       nb++;
       in_step++;
       int any = 0;
-      for (int l = 0; l < 16 && !any; l++) {
+      for (int l = 0; l < 16; l++) {
         int px = sx + (l & 3), py = sy + (l >> 2);
         hit_t h;
+        if (!(b[2] > py || b[3] < py || floor(((double)px - b[0]) * ip) < ceil(((double)px - b[1]) * ip)))
+          inbox++;
         if (px < W && py < H && intersect(&rays[l], (float)px, (float)py, T + 12 * (size_t)id,
-                                          xy + 2 * (size_t)id, nrm_opa[4 * (size_t)id + 3], &h)) any = 1;
+                                          xy + 2 * (size_t)id, nrm_opa[4 * (size_t)id + 3], &h)) {
+          any = 1;
+          okpix++;
+        }
       }
       nt += any;
     }
     pairs += (in_step + 1) / 2; busy += in_step > 0;
-    out[5 * st] = trav; out[5 * st + 1] = nb; out[5 * st + 2] = nt; out[5 * st + 3] = pairs; out[5 * st + 4] = busy;
+    out[7 * st] = trav; out[7 * st + 1] = nb; out[7 * st + 2] = nt; out[7 * st + 3] = pairs; out[7 * st + 4] = busy;
+    out[7 * st + 5] = inbox; out[7 * st + 6] = okpix;
   }
 }

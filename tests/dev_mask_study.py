@@ -125,15 +125,18 @@ def main(cfg):
             boxes = np.ascontiguousarray(fn(T.astype(np.float64), no[:, 3].astype(np.float64),
                                             xy.astype(np.float64), fx, fy, cy), np.float32)
         boxes[~np.isfinite(boxes).all(1)] = [-1e30, 1e30, -1e30, 1e30]
-        out = np.zeros(nsub * 5, np.uint32)
+        out = np.zeros(nsub * 7, np.uint32)
         ranges = np.ascontiguousarray(f["ranges"], np.uint32)
         pl = np.ascontiguousarray(f["point_list"], np.uint32)
         nc = np.ascontiguousarray(f["n_contrib"], np.uint32)
         L.orc_subtile_stats(W, H, p(ranges), p(pl), p(xy), p(T), p(no), p(Pm), p(nc), p(boxes), p(out))
-        o = out.reshape(-1, 5).astype(np.int64)
+        o = out.reshape(-1, 7).astype(np.int64)
         res[name] = o
         print(f"{name:8s}: two-at-a-time steps {o[:, 3].sum()} for {o[:, 1].sum()} visits "
               f"(ideal {(o[:, 1].sum() + 1) // 2}); 32-entry steps with a visit {o[:, 4].sum()} of {((o[:, 0] + 31) // 32).sum()}")
+        print(f"{name:8s}: (pixel, visit) pairs {16 * o[:, 1].sum()}: pixel inside the box {o[:, 5].sum()} "
+              f"({100 * o[:, 5].sum() / (16 * o[:, 1].sum()):.0f} %), pass the alpha test {o[:, 6].sum()} "
+              f"({100 * o[:, 6].sum() / (16 * o[:, 1].sum()):.0f} %)")
         print(f"{name:8s}: traversed {o[:, 0].sum():>10d}  visited {o[:, 1].sum():>10d}  true {o[:, 2].sum():>10d}"
               f"  (per sub-tile {o[:, 0].mean():.0f} / {o[:, 1].mean():.0f} / {o[:, 2].mean():.0f})")
     a, b = res["sphere"], res["ellipse"]
