@@ -569,7 +569,9 @@ def run_reference(args, rank, world, local_rank):
         torch.cuda.synchronize()
         return sum(a.elapsed_time(b) for a, b in ev) / args.steps
 
+    sampler = ClockSampler(local_rank)
     ms = timed(lambda: frame(t, opa))
+    line["clocks"] = sampler.stop()
     hp = scene_tensors(args.config, 0, dev, pinned=True)
     keys = ("means3D", "opacities", "scales", "rotations", "dL_dout")
 
