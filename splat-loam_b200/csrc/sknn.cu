@@ -22,7 +22,10 @@
 
 namespace {
 
-constexpr int LEAF = 32;
+#ifndef KNN_LEAF
+#define KNN_LEAF 16
+#endif
+constexpr int LEAF = KNN_LEAF;   // points per leaf box (divides 32); a warp of queries = 32 / LEAF leaves
 constexpr int FAN = 8;
 constexpr int MAXL = 12;
 #ifndef KNN_NEAR
@@ -214,13 +217,20 @@ gather_leaf_kernel(int P, const float *__restrict__ pts,
     z = pts[3 * (size_t)idx + 2];
     sorted[i] = make_float4(x, y, z, __uint_as_float(idx));
   }
-  const float lx = warp_min(have ? x : FLT_MAX), ly = warp_min(have ? y : FLT_MAX),
-              lz = warp_min(have ? z : FLT_MAX);
-  const float hx = warp_max(have ? x : -FLT_MAX), hy = warp_max(have ? y : -FLT_MAX),
-              hz = warp_max(have ? z : -FLT_MAX);
-  if ((threadIdx.x & 31) == 0 && have) {
-    boxes[2 * (size_t)(i >> 5)] = make_float4(lx, ly, lz, 0.f);
-    boxes[2 * (size_t)(i >> 5) + 1] = make_float4(hx, hy, hz, 0.f);
+  float lx = have ? x : FLT_MAX, ly = have ? y : FLT_MAX, lz = have ? z : FLT_MAX;
+  float hx = have ? x : -FLT_MAX, hy = have ? y : -FLT_MAX, hz = have ? z : -FLT_MAX;
+#pragma unroll
+  for (int o = LEAF / 2; o > 0; o >>= 1) {   // min / max over the LEAF lanes of a leaf
+    lx = fminf(lx, __shfl_xor_sync(0xffffffffu, lx, o));
+    ly = fminf(ly, __shfl_xor_sync(0xffffffffu, ly, o));
+    lz = fminf(lz, __shfl_xor_sync(0xffffffffu, lz, o));
+    hx = fmaxf(hx, __shfl_xor_sync(0xffffffffu, hx, o));
+    hy = fmaxf(hy, __shfl_xor_sync(0xffffffffu, hy, o));
+    hz = fmaxf(hz, __shfl_xor_sync(0xffffffffu, hz, o));
+  }
+  if ((threadIdx.x & (LEAF - 1)) == 0 && have) {
+    boxes[2 * (size_t)(i / LEAF)] = make_float4(lx, ly, lz, 0.f);
+    boxes[2 * (size_t)(i / LEAF) + 1] = make_float4(hx, hy, hz, 0.f);
   }
 }
 
@@ -259,21 +269,20 @@ __global__ void __launch_bounds__(128)
 query_kernel(int P, const float4 *__restrict__ sorted, const float4 *__restrict__ boxes,
              KnnLevels lv, float *__restrict__ out) {
   const int i = blockIdx.x * 128 + threadIdx.x;
-  const uint32_t own = (uint32_t)i >> 5;                 // warp-uniform
-  if ((int)(own * LEAF) >= P) return;                     // whole warp past the end
+  const int wbase = i & ~31;                               // warp-uniform: first query of the warp
+  if (wbase >= P) return;                                 // whole warp past the end
   const bool live = i < P;
   const float4 q = sorted[live ? i : P - 1];
   float b0 = FLT_MAX, b1 = FLT_MAX, b2 = FLT_MAX;
-  // own leaf and its neighbours in Morton order first: they tighten the bound before the descent
-  const uint32_t near_lo = own > NEAR ? own - NEAR : 0u;
-  const uint32_t near_hi = min(own + NEAR, (uint32_t)lv.cnt[0] - 1u);
-  {
-    const int s = near_lo * LEAF, e = min(P, (int)(near_hi + 1) * LEAF);
-    for (int j = s; j < e; j++) {
-      const float4 p = sorted[j];
-      if (j != i) update3(q, p, b0, b1, b2);
-    }
+  // the warp's own points and their neighbours in Morton order first: they tighten the bound
+  // before the descent
+  const int plo = max(0, wbase - 32 * (int)NEAR), phi = min(P, wbase + 32 * ((int)NEAR + 1));
+  for (int j = plo; j < phi; j++) {
+    const float4 p = sorted[j];
+    if (j != i) update3(q, p, b0, b1, b2);
   }
+  const uint32_t near_lo = (uint32_t)plo / LEAF;          // leaves [near_lo, near_hi] are done
+  const uint32_t near_hi = (uint32_t)(phi - 1) / LEAF;
   uint32_t cur[MAXL], end[MAXL];
   int lvl = lv.nlevel - 1;
   cur[lvl] = 0;
