@@ -175,3 +175,15 @@ def test_stress_geometry_matches_reference(native_lib, seed):
     a sub-tile mask that dropped a contributing surfel anywhere would change a pixel."""
     s = _stress_scene(seed)
     _compare(_product(s), _reference(s), s["H"] * s["W"])
+
+
+@pytest.mark.parametrize("P", [300000])
+def test_sort_with_16_keys_per_thread_matches_reference(native_lib, P):
+    """The sort picks 8, 12 or 16 keys per thread from the expected instance count (C0/C1 run
+    with 8, C2 with 12); ~1.05 M instances is the range where 16 fills one wave."""
+    s = scenes.make_scene((64, 1024, 33.2, P))
+    r, g = _product(s), _reference(s)
+    assert 909000 < r["num_rendered"] < 1210000, r["num_rendered"]
+    _compare(r, g, s["H"] * s["W"])
+    r2 = _product(s)           # second frame: sized from the previous frame's count (hint path)
+    _compare(r2, g, s["H"] * s["W"])
