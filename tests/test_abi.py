@@ -87,3 +87,17 @@ def test_missing_library_fails_loudly(native_lib, tmp_path, monkeypatch):
     monkeypatch.setattr(n, "LIB_PATH", str(tmp_path / "nope.so"))
     with pytest.raises(ImportError, match="no CPU or PyTorch fallback"):
         n.load()
+
+
+def test_header_is_plain_c_and_cpp():
+    """The drop-in boundary must be bindable from C (cgo / ctypes / JNI style FFI) as well as
+    C++: the header compiles as C99 and as C++11 with warnings as errors."""
+    import shutil
+    import subprocess
+    hdr = os.path.join(ROOT, "include", "splat_b200.h")
+    for cc, lang, std in (("gcc", "c", "-std=c99"), ("g++", "c++", "-std=c++11")):
+        if shutil.which(cc) is None:
+            pytest.skip(f"{cc} not installed")
+        p = subprocess.run([cc, std, "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only",
+                            "-x", lang, hdr], capture_output=True, text=True)
+        assert p.returncode == 0, p.stderr
