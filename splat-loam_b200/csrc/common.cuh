@@ -306,7 +306,7 @@ static inline bool first_use_on_device(unsigned long long &seen) {
   seen |= bit;
   return true;
 }
-void launch_bwd_order(const ImageView &im, cudaStream_t s);
+void launch_bwd_order(const ImageView &im, void *fill, size_t fill_bytes, cudaStream_t s);
 void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageView &im,
                            const BinView &b, uint32_t capacity, cudaStream_t s);
 

@@ -290,6 +290,8 @@ int dssr_backward(const dssr_backward_args *a) {
     return fail("dssr_backward: scales / dL_dscales must be 8-byte and rotations / "
                 "dL_drotations / dL_dtransMat 16-byte aligned");
   const bool dbg = a->debug & 1;
+  char *fused_fill = nullptr;
+  size_t fused_bytes = 0;
   {
     // the four accumulation targets must start at zero; when the caller laid them out back to
     // back (as _C.py does, one allocation) that is ONE fill instead of four
@@ -302,7 +304,14 @@ int dssr_backward(const dssr_backward_args *a) {
       if (ptr[i] + len[i] > hi) hi = ptr[i] + len[i];
     }
     if ((size_t)(hi - lo) <= 76 * P + 4096) {
-      CUDA_TRY(cudaMemsetAsync(lo, 0, (size_t)(hi - lo), st));
+      if (((uintptr_t)lo & 15) == 0) {   // zeroed by the work-order launch below
+        fused_fill = lo;
+        fused_bytes = (size_t)(hi - lo) & ~(size_t)15;
+        if (fused_bytes != (size_t)(hi - lo))
+          CUDA_TRY(cudaMemsetAsync(lo + fused_bytes, 0, (size_t)(hi - lo) - fused_bytes, st));
+      } else {
+        CUDA_TRY(cudaMemsetAsync(lo, 0, (size_t)(hi - lo), st));
+      }
     } else {
       for (int i = 0; i < 4; i++) CUDA_TRY(cudaMemsetAsync(ptr[i], 0, len[i], st));
     }
@@ -331,7 +340,8 @@ int dssr_backward(const dssr_backward_args *a) {
   }
   {
     ProfScope ps("render_backward", st);
-    launch_bwd_order(iv, st);   // here, not in the forward: forward-only renders do not pay for it
+    // here, not in the forward: forward-only renders do not pay for it
+    launch_bwd_order(iv, fused_fill, fused_bytes, st);
     launch_render_backward(bp, gv, iv, bv, st);
   }
   LAUNCH_CHECK(dbg, st, "render_backward");

@@ -254,9 +254,19 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
 // the number of entries they walk (correlation 0.85, against 0.35 for the tile's list length),
 // so longest-first numbering packs the waves: list scheduling of the measured warp times gave
 // 363 us against 618 us for the tile-length order.
+// Blocks 1.. of the same launch zero the backward's accumulation buffers (`fill`, n16 16-byte
+// words) meanwhile: one launch instead of a fill and a kernel one after the other.
 constexpr int COST_BINS = 2048;
 __global__ void __launch_bounds__(1024)
-bwd_order_kernel(const uint32_t *__restrict__ sub_cost, int units, uint32_t *__restrict__ order) {
+bwd_order_kernel(const uint32_t *__restrict__ sub_cost, int units, uint32_t *__restrict__ order,
+                 float4 *__restrict__ fill, size_t n16) {
+  if (blockIdx.x > 0) {
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (size_t k = (size_t)(blockIdx.x - 1) * 1024 + threadIdx.x; k < n16;
+         k += (size_t)(gridDim.x - 1) * 1024)
+      fill[k] = z;
+    return;
+  }
   __shared__ uint32_t s_bin[COST_BINS];
   __shared__ uint32_t s_warp[32];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -288,8 +298,11 @@ bwd_order_kernel(const uint32_t *__restrict__ sub_cost, int units, uint32_t *__r
 
 }  // namespace
 
-void launch_bwd_order(const ImageView &im, cudaStream_t s) {
-  bwd_order_kernel<<<1, 1024, 0, s>>>(im.sub_cost, im.tiles * SUBS_PER_TILE, im.bwd_order);
+// `fill` (16-byte aligned, fill_bytes a multiple of 16) is zeroed by the same launch; nullptr: no fill
+void launch_bwd_order(const ImageView &im, void *fill, size_t fill_bytes, cudaStream_t s) {
+  const int fill_blocks = fill ? 296 : 0;
+  bwd_order_kernel<<<1 + fill_blocks, 1024, 0, s>>>(im.sub_cost, im.tiles * SUBS_PER_TILE,
+                                                    im.bwd_order, (float4 *)fill, fill_bytes / 16);
 }
 
 void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageView &im,
