@@ -101,3 +101,26 @@ def test_header_is_plain_c_and_cpp():
         p = subprocess.run([cc, std, "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only",
                             "-x", lang, hdr], capture_output=True, text=True)
         assert p.returncode == 0, p.stderr
+
+
+def test_widened_surfaces_reject_cpu_tensors(native_lib):
+    """gaussian_renderer / mapping_loss / fused_adam have no CPU path either: CPU tensors are an
+    error, not a silent fallback."""
+    import torch
+    import gaussian_renderer as gr
+    import mapping_loss as ml
+    from fused_adam import activation_adam_step
+    with pytest.raises(RuntimeError, match="must be a CUDA tensor"):
+        gr.postprocess(torch.zeros(7, 4, 4), torch.eye(4), torch.eye(4), 0.0)
+
+    class Cam:
+        world_view_transform = torch.eye(4)
+        projection_matrix = torch.eye(4)
+        image_depth = torch.zeros(1, 4, 4)
+        image_valid = torch.ones(1, 4, 4, dtype=torch.uint8)
+    with pytest.raises(RuntimeError, match="must be a CUDA tensor"):
+        ml.mapping_image_losses(torch.zeros(7, 4, 4), Cam)
+    p = torch.nn.Parameter(torch.zeros(4, 3))
+    opt = torch.optim.Adam([{"params": [p], "name": "xyz"}], lr=1e-3)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        activation_adam_step(opt, torch.zeros(4, 10))
