@@ -44,13 +44,32 @@ class PeerExchange:
         self.group, self.P, self.device = group, int(P), torch.device(device)
         rank, world = dist.get_rank(group), dist.get_world_size(group)
         self.handle = ctypes.c_void_p()
+        self.result = None
         with torch.cuda.device(self.device):
-            native.check(self._lib.splat_xchg_create(self.P, world, rank, ctypes.byref(self.handle)))
-            mine = ctypes.create_string_buffer(native.XCHG_HANDLE_BYTES)
-            native.check(self._lib.splat_xchg_export(self.handle, mine))
+            # every step is agreed on by all ranks before the next collective call: a rank whose
+            # device cannot export or map peer memory must not leave the others waiting
+            err, mine = "", ctypes.create_string_buffer(native.XCHG_HANDLE_BYTES)
+            try:
+                native.check(self._lib.splat_xchg_create(self.P, world, rank,
+                                                         ctypes.byref(self.handle)))
+                native.check(self._lib.splat_xchg_export(self.handle, mine))
+            except RuntimeError as e:
+                err = str(e)
             handles = [None] * world
-            dist.all_gather_object(handles, mine.raw, group=group)
-            native.check(self._lib.splat_xchg_connect(self.handle, b"".join(handles)))
+            dist.all_gather_object(handles, (err, mine.raw), group=group)
+            errs = [h[0] for h in handles if h[0]]
+            if not errs:
+                try:
+                    native.check(self._lib.splat_xchg_connect(
+                        self.handle, b"".join(h[1] for h in handles)))
+                except RuntimeError as e:
+                    err = str(e)
+                flags = [None] * world
+                dist.all_gather_object(flags, err, group=group)
+                errs = [f for f in flags if f]
+            if errs:
+                self.close()
+                raise RuntimeError("peer-memory exchange unavailable: " + errs[0])
             ptr = self._lib.splat_xchg_result(self.handle)
             self.result = torch.as_tensor(_DeviceArray(ptr, (self.P, GRAD_COLS), self),
                                           device=self.device)
@@ -127,7 +146,16 @@ class KeyframeWindow:
         if self._xchg is None or self._xchg.P != P or self._xchg.device != device:
             if self._xchg is not None:
                 self._xchg.close()
-            self._xchg = PeerExchange(P, device, self.group)
+                self._xchg = None
+            try:
+                self._xchg = PeerExchange(P, device, self.group)
+            except RuntimeError as e:
+                if self.exchange != "auto":
+                    raise
+                import sys
+                print(f"[keyframe_window] {e}; using the process group's all-reduce", file=sys.stderr)
+                self.exchange = "collective"       # agreed by all ranks (see PeerExchange)
+                return None
         return self._xchg
 
     def _world(self):
