@@ -3,12 +3,17 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config C2]
 
-A "step" is one pass of the hot path over one synthetic frame: rasterizer forward +
+A "step" is one pass of the hot path over one synthetic frame per GPU: rasterizer forward +
 backward through the reference-facing `_C` calls (which go through the C-ABI of
 libsplat_b200.so).  N=1 runs BASELINE config C2 (64x1024 image, 500k surfels).  N>1 is the
-keyframe-sharded window (weak scaling): every rank renders its own keyframe of the same
-surfel set and the per-surfel [P,10] gradient buffers are summed over NVLink peer memory
-(push fused into the VJP kernel; SPLAT_B200_XCHG=nccl selects one NCCL all-reduce instead).
+keyframe-sharded window (weak scaling): rank r renders keyframe r (BASELINE poses: 0.5 m and
+2 degrees of yaw per keyframe) of the same surfel set and the per-surfel [P,10] gradient
+buffers are summed over NVLink peer memory (push fused into the VJP kernel;
+SPLAT_B200_XCHG=nccl selects one NCCL all-reduce instead); before anything is timed the
+exchange's sum is checked against an NCCL all-reduce of the same buffers
+(`exchange_check`).  At N>1 the line also carries `window`: the BASELINE window configs
+(C3: 8 keyframes at 2/4/8 GPUs, C4: 32 keyframes at 8) through KeyframeWindow.gradients,
+with the same window timed on ONE GPU in the same run.
 
 Rank 0 prints ONE JSON line.  See DESIGN.md "Measurement" for every field.
 """
@@ -122,17 +127,39 @@ class ClockSampler:
 
 
 def scene_tensors(cfg, keyframe, device, pinned=False):
-    # weak scaling wants the same work on every GPU: the keyframes of the window differ by a
-    # pure rotation about the sensor's vertical axis (22.5 degrees per keyframe), which leaves
-    # ranges and footprints - hence the cost of a frame - statistically unchanged
-    s = scenes.make_scene(cfg, keyframe=0)
-    s["viewmatrix"] = scenes.yaw_viewmatrix(22.5 * keyframe)
+    # keyframe k of the window: BASELINE.md section 3's poses (0.5 m * k along x, 2 deg * k of
+    # yaw) over ONE surfel set (seed 0) - the frames of a window do not cost exactly the same
+    s = scenes.make_scene(cfg, keyframe=keyframe)
     t = {}
     for k in ("means3D", "opacities", "scales", "rotations", "viewmatrix", "projmatrix", "dL_dout"):
         x = torch.from_numpy(s[k])
         t[k] = x.pin_memory() if pinned else x.to(device)
     t["H"], t["W"] = s["H"], s["W"]
     return t
+
+
+def workload(cfg, H, W, P):
+    """The same string for both arms (the implementation goes under config.implementation)."""
+    return (f"{cfg}: {H}x{W} spherical range image, {P} surfels, fwd+bwd per frame, one keyframe "
+            "per GPU (keyframe r on rank r)")
+
+
+L2_NOTE = "192 MB buffer (1.5x the 126 MB L2) written between timed steps"
+
+
+def timed_steps(step_fn, steps, flush, barrier):
+    """The timed region of both arms: a barrier + synchronize on both sides, the L2 flush
+    outside each step's event pair, CUDA events on the current stream.  Returns total ms."""
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+          for _ in range(steps)]
+    barrier()
+    for a, b in ev:
+        flush.zero_()                     # L2 flush between timed iterations (not timed)
+        a.record()
+        step_fn()
+        b.record()
+    barrier()
+    return sum(a.elapsed_time(b) for a, b in ev)
 
 
 def algorithmic_bytes(P, N, Nc, HW):
@@ -158,20 +185,16 @@ def consumed_instances(nc, ranges, H, W):
     return int(pad.reshape(gy, 16, gx, 16).max(axis=(1, 3)).sum())
 
 
-def pipelined_e2e(dev, hp, keys, steps, flush, frame_fn, out_specs):
-    """End-to-end protocol shared by both arms: every step copies that step's inputs from
-    pinned host memory, runs `frame_fn(device_inputs, slot)` -> list of device result tensors,
-    and copies the results back to pinned host memory, all inside the timed region.  Inputs,
-    results and host buffers are double-buffered so the copies of neighbouring steps overlap
-    the compute (copy engines on side streams); the L2 flush is also inside the timed region.
-    Returns average milliseconds per step (CUDA events on the compute stream)."""
+def pipelined_e2e(dev, steps, flush, copy_in, frame_fn, out_specs):
+    """End-to-end protocol shared by both arms: every step brings that step's inputs from
+    pinned host memory into device slot b (`copy_in(b)`, enqueued on a side stream: H2D copies
+    and, for a sharded upload, the all-gather that completes them), runs `frame_fn(b)` -> list
+    of device result tensors, and copies the results back to pinned host memory, all inside
+    the timed region.  Inputs, results and host buffers are double-buffered so the copies of
+    neighbouring steps overlap the compute (copy engines on side streams); the L2 flush is
+    also inside the timed region.  Returns (ms per step, D2H bytes per step)."""
     main = torch.cuda.current_stream(dev)
     s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
-    d_in = [{k: torch.empty_like(hp[k], device=dev) for k in keys} for _ in range(2)]
-    for b in range(2):
-        for k, v in hp.items():
-            if torch.is_tensor(v) and k not in keys:
-                d_in[b][k] = v.to(dev)
     h_out = [[torch.empty(sh, dtype=torch.float32).pin_memory() for sh in out_specs] for _ in range(2)]
     ev_in = [torch.cuda.Event() for _ in range(2)]
     ev_used = [torch.cuda.Event() for _ in range(2)]
@@ -184,14 +207,13 @@ def pipelined_e2e(dev, hp, keys, steps, flush, frame_fn, out_specs):
             with torch.cuda.stream(s_in):
                 if i >= 2:
                     s_in.wait_event(ev_used[b])        # the frame two steps ago has read them
-                for k in keys:
-                    d_in[b][k].copy_(hp[k], non_blocking=True)
+                copy_in(b)
                 ev_in[b].record(s_in)
             main.wait_event(ev_in[b])
             if i >= 2:
                 main.wait_event(ev_out[b])             # result slot b has been drained
             flush.zero_()
-            res = frame_fn(d_in[b], b)
+            res = frame_fn(b)
             ev_used[b].record(main)
             ev_res[b].record(main)
             with torch.cuda.stream(s_out):
@@ -211,8 +233,10 @@ def pipelined_e2e(dev, hp, keys, steps, flush, frame_fn, out_specs):
     run(steps)
     z.record(main)
     z.synchronize()
-    return a.elapsed_time(z) / steps, sum(hp[k].numel() * 4 for k in keys), \
-        sum(h.numel() * 4 for h in h_out[0])
+    return a.elapsed_time(z) / steps, sum(h.numel() * 4 for h in h_out[0])
+
+
+PARAM_KEYS = ("means3D", "opacities", "scales", "rotations")
 
 
 # ------------------------------------------------------------------ our arm ------------
@@ -240,7 +264,7 @@ def run_ours(args, rank, world, local_rank):
             if rank == 0:
                 print(f"[bench] {e}; falling back to the NCCL all-reduce", file=sys.stderr)
 
-    def frame(x):
+    def fwd_bwd(x, packed=None, use_xchg=False):
         R, allmap, radii, geom, binning, img = _C.rasterize_gaussians(
             x["means3D"], x["opacities"], x["scales"], x["rotations"], 1.0, empty,
             x["viewmatrix"], x["projmatrix"], H, W, False, False)
@@ -248,12 +272,18 @@ def run_ours(args, rank, world, local_rank):
         g = _C.rasterize_gaussians_backward(
             x["means3D"], radii, x["scales"], x["rotations"], 1.0, empty, x["viewmatrix"],
             x["projmatrix"], x["dL_dout"], geom, R, binning, img, False,
-            packed=None if xchg else gbuf, xchg=xchg.handle.value if xchg else None)
-        if xchg:
-            xchg.allreduce()
-        elif world > 1:
-            dist.all_reduce(gbuf)
+            packed=packed, xchg=xchg.handle.value if use_xchg else None)
         return R, allmap, g, (geom, binning, img)
+
+    def frame(x):
+        if xchg:
+            out = fwd_bwd(x, None, True)
+            xchg.allreduce()
+        else:
+            out = fwd_bwd(x, gbuf)
+            if world > 1:
+                dist.all_reduce(gbuf)
+        return out
 
     def barrier():
         if world > 1:
@@ -267,6 +297,31 @@ def run_ours(args, rank, world, local_rank):
     nc = _C.debug_state(*bufs, "n_contrib").numpy().view(np.uint32)
     rg = _C.debug_state(*bufs, "ranges").numpy()
     Nc = consumed_instances(nc, rg, H, W)
+
+    # ---- N>1: the exchange's sum against an NCCL all-reduce of the same buffers -------
+    exchange_check = None
+    if world > 1:
+        fwd_bwd(t, gbuf)                              # this rank's [P,10], no exchange
+        want = gbuf.clone()
+        dist.all_reduce(want)
+        if xchg:
+            fwd_bwd(t, None, True)
+            got = xchg.allreduce().clone()
+            xchg.check()
+        else:
+            got = want.clone()
+        rel = float((got.double() - want.double()).norm() / want.double().norm())
+        ref0 = got.clone()
+        dist.broadcast(ref0, src=0)
+        same = torch.tensor([1 if torch.equal(ref0, got) else 0], device=dev)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        relt = torch.tensor([rel], device=dev, dtype=torch.float64)
+        dist.all_reduce(relt, op=dist.ReduceOp.MAX)
+        exchange_check = {"rel_err": float(relt[0]), "bit_identical_across_ranks": bool(same[0]),
+                          "against": "dist.all_reduce (NCCL) of the same per-rank [P,10] buffers",
+                          "path": "peer memory" if xchg else "nccl (nothing to compare)"}
+        assert exchange_check["rel_err"] < 1e-5 and exchange_check["bit_identical_across_ranks"], \
+            exchange_check
 
     # ---- per-stage times (instrumented pass: every stage bracketed by events) ----
     native.profile_enable(True)
@@ -283,44 +338,81 @@ def run_ours(args, rank, world, local_rank):
     # pair (the roofline's launch duration is measured inside this timed region) ----
     sampler = ClockSampler(local_rank) if rank == 0 else None
     native.profile_enable(True, only=dom)
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-          for _ in range(args.steps)]
-    barrier()
-    for a, b in ev:
-        flush.zero_()                     # L2 flush between timed iterations (not timed)
-        a.record()
-        frame(t)
-        b.record()
-    barrier()
+    launches0 = native.launch_count()
+    total_ms = timed_steps(lambda: frame(t), args.steps, flush, barrier)
+    launches = native.launch_count() - launches0
     dom_ms = native.profile_read().get(dom, 0.0) / args.steps
     native.profile_enable(False)
-    total_ms = sum(a.elapsed_time(b) for a, b in ev)
     clocks = sampler.stop() if sampler else None
 
+    # ---- the same through the reference's stock 14-argument backward (no packed=) ----
+    stock_ms = None
+    if world == 1:
+        stock_ms = timed_steps(lambda: fwd_bwd(t), args.steps, flush, barrier) / args.steps
+
     # ---- end to end through the same calls with HOST buffers ----
+    # N = 1: the frame's parameters, dL_dout in; maps and [P,10] gradients out.  N > 1: the
+    # parameters are replicated, so each rank uploads 1/N of their rows and the ranks all-gather
+    # them over NVLink; every rank uploads its own keyframe's dL_dout, downloads its own maps
+    # and the slice of the summed gradients it owns in the exchange.  The byte counts are the
+    # whole job's.
     hp = scene_tensors(args.config, rank, dev, pinned=True)
-    keys = ("means3D", "opacities", "scales", "rotations", "dL_dout")
-    gbufs = [gbuf, torch.empty_like(gbuf)]
+    rows = (P + world - 1) // world
+    if xchg:
+        rows = (rows + 255) // 256 * 256              # the exchange's slice (XCHG_SLICE_ALIGN)
+    lo, hi = min(P, rank * rows), min(P, (rank + 1) * rows)
+    shard = world > 1 and P % world == 0
+    d_in = []
+    for b in range(2):
+        d = {k: torch.empty_like(hp[k], device=dev) for k in PARAM_KEYS + ("dL_dout",)}
+        d["viewmatrix"], d["projmatrix"] = t["viewmatrix"], t["projmatrix"]
+        d_in.append(d)
+    if shard:
+        per = P // world
+        h_slice = {k: hp[k][rank * per:(rank + 1) * per].clone().pin_memory() for k in PARAM_KEYS}
+        d_slice = [{k: torch.empty_like(h_slice[k], device=dev) for k in PARAM_KEYS} for _ in range(2)]
 
-    def e2e_frame(x, slot):
-        R, allmap, radii, geom, binning, img = _C.rasterize_gaussians(
-            x["means3D"], x["opacities"], x["scales"], x["rotations"], 1.0, empty,
-            x["viewmatrix"], x["projmatrix"], H, W, False, False)
-        _C.rasterize_gaussians_backward(
-            x["means3D"], radii, x["scales"], x["rotations"], 1.0, empty, x["viewmatrix"],
-            x["projmatrix"], x["dL_dout"], geom, R, binning, img, False,
-            packed=None if xchg else gbufs[slot], xchg=xchg.handle.value if xchg else None)
-        if xchg:      # the exchange owns ONE result array: park it in this step's slot
-            gbufs[slot].copy_(xchg.allreduce())
-        elif world > 1:
-            dist.all_reduce(gbufs[slot])
-        return [allmap, gbufs[slot]]
+    def copy_in(b):
+        d_in[b]["dL_dout"].copy_(hp["dL_dout"], non_blocking=True)
+        if shard:
+            for k in PARAM_KEYS:
+                d_slice[b][k].copy_(h_slice[k], non_blocking=True)
+                dist.all_gather_into_tensor(d_in[b][k], d_slice[b][k])
+        else:
+            for k in PARAM_KEYS:
+                d_in[b][k].copy_(hp[k], non_blocking=True)
+
+    gslots = [torch.empty((hi - lo, 10), dtype=torch.float32, device=dev) for _ in range(2)]
+    gfull = [gbuf, torch.empty_like(gbuf)]
+
+    def e2e_frame(b):
+        x = d_in[b]
+        if xchg:       # the exchange owns ONE result array: park the owned slice in the slot
+            _, allmap, _, _ = fwd_bwd(x, None, True)
+            gslots[b].copy_(xchg.allreduce()[lo:hi])
+            return [allmap, gslots[b]]
+        _, allmap, _, _ = fwd_bwd(x, gfull[b])
+        if world > 1:
+            dist.all_reduce(gfull[b])
+            gslots[b].copy_(gfull[b][lo:hi])
+            return [allmap, gslots[b]]
+        return [allmap, gfull[b]]
 
     barrier()
-    e2e_ms_step, h2d, d2h = pipelined_e2e(dev, hp, keys, args.steps, flush, e2e_frame,
-                                          [(7, H, W), (P, 10)])
+    e2e_ms_step, d2h = pipelined_e2e(dev, args.steps, flush, copy_in, e2e_frame,
+                                     [(7, H, W), (hi - lo, 10)])
     barrier()
+    if xchg:
+        xchg.check()
     e2e_ms = e2e_ms_step * args.steps
+    h2d = 7 * H * W * 4 * world + P * 10 * 4 if shard else (7 * H * W + P * 10) * 4 * world
+    d2h_job = 7 * H * W * 4 * world + P * 10 * 4 if world > 1 else d2h
+
+    window = None
+    if world > 1 and not args.no_window:
+        window = [run_window("C3", 8, rank, world, dev, flush)]
+        if world >= 8:
+            window.append(run_window("C4", 32, rank, world, dev, flush))
 
     if world > 1:   # max over ranks, on the device timeline
         tt = torch.tensor([total_ms, e2e_ms], device=dev, dtype=torch.float64)
@@ -346,36 +438,51 @@ def run_ours(args, rank, world, local_rank):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.config}: {H}x{W} spherical range image, {P} surfels, "
-                               f"fwd+bwd per frame, one keyframe per GPU"
-                               + ((", [P,10] gradients summed over NVLink peer memory (push "
-                                   "fused into the VJP kernel)" if xchg else
-                                   ", NCCL all-reduce of the [P,10] gradients")
-                                  if world > 1 else ""),
-                   "instances": R, "consumed_instances": Nc,
-                   "l2": "192 MB buffer (1.5x the 126 MB L2) written between timed steps",
+        "config": {"workload": workload(args.config, H, W, P),
+                   "implementation": "libsplat_b200.so through the drop-in _C surface",
+                   "exchange": (("[P,10] gradients summed over NVLink peer memory (push fused "
+                                 "into the VJP kernel)" if xchg else
+                                 "NCCL all-reduce of the [P,10] gradients")
+                                if world > 1 else "none (one GPU)"),
+                   "instances": R, "consumed_instances": Nc, "l2": L2_NOTE,
                    "parallelism": f"keyframe-sharded x{world}"},
         "e2e": {"value": world * 1e3 / (e2e_ms / args.steps), "unit": UNIT,
-                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-        # 9 forward (preprocess, chunk scan, emit, digit scan, 4 sort passes, render) + 3 backward
-        # kernels (work order, render, per-surfel VJP) per frame (+ the exchange's reduce kernel)
-        "gpu_launches": (13 if xchg else 12) * args.steps,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h_job,
+                "note": ("whole-job bytes; parameters uploaded 1/N per rank and all-gathered over "
+                         "NVLink, each rank downloads its maps and its owned gradient slice")
+                if shard else "whole-job bytes"},
+        # counted by the library (splat_launch_count) over the timed region, all of rank 0's
+        # kernels: per frame 9 forward + 3 backward (+ the exchange's reduce kernel)
+        "gpu_launches": launches,
         "stage_ms": stage_ms,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak,
                      "peak_source": peak_src, "unit": "GB/s",
                      "frac": achieved / peak if achieved else None, "traffic": traffic,
+                     "traffic_source": "profiles/traffic.json (ncu --set full of an earlier "
+                                       "session, a constant - not measured by this run)",
                      "algorithmic_bytes": ab[dom]},
         "frame_roofline": {"algorithmic_bytes": ab["frame"],
                            "achieved": ab["frame"] / (ms_per_step * 1e-3) / 1e9, "unit": "GB/s",
                            "frac": ab["frame"] / (ms_per_step * 1e-3) / 1e9 / peak},
         "clocks": clocks,
     }
+    if stock_ms:
+        line["stock_signature"] = {
+            "value": 1e3 / stock_ms, "unit": UNIT, "ms_per_step": stock_ms,
+            "what": "the same frames through the reference's 14-argument "
+                    "rasterize_gaussians_backward (no packed= extension)"}
+    if exchange_check:
+        line["exchange_check"] = exchange_check
+    if window:
+        line["window"] = window
     if winst and stage_ms.get(dom) and clocks and clocks.get("sm_mhz"):
         # the compositing kernels are bound by instruction issue, not by HBM: warp instructions
         # per launch (ncu, profiles/) / live launch duration, against 4 issue slots per SM and clock
         sms = torch.cuda.get_device_properties(dev).multi_processor_count
         ipeak = sms * 4 * clocks["sm_mhz"] * 1e6
         line["issue_roofline"] = {"kernel": dom, "warp_instructions": winst,
+                                  "warp_instructions_source": "profiles/traffic.json (session "
+                                                              "constant, ncu smsp__inst_executed)",
                                   "achieved": winst / (stage_ms[dom] * 1e-3), "peak": ipeak,
                                   "unit": "warp-inst/s", "frac": winst / (stage_ms[dom] * 1e-3) / ipeak}
     if world == 1:
@@ -384,6 +491,57 @@ def run_ours(args, rank, world, local_rank):
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args.config)
     return line
+
+
+def run_window(cfg, K, rank, world, dev, flush, reps=10):
+    """a window of K keyframes of `cfg` (BASELINE poses) through
+    KeyframeWindow.gradients, sharded over the ranks, and the same window on ONE GPU (every
+    rank runs it alone, at the same time, without communication) - all in this run.
+    t = milliseconds per window, max over ranks; of_linear = t(1 GPU) / (G * t(G GPUs))."""
+    import torch.distributed as dist
+    from keyframe_window import KeyframeWindow
+    s = scenes.make_scene(cfg)
+    H, W = s["H"], s["W"]
+    params = tuple(torch.from_numpy(s[k]).to(dev) for k in PARAM_KEYS)
+    proj = torch.from_numpy(s["projmatrix"]).to(dev)
+    cams = [(torch.from_numpy(scenes.viewmatrix(k)).to(dev), proj, H, W) for k in range(K)]
+    dL = torch.from_numpy(s["dL_dout"]).to(dev)
+    up = lambda k, allmap: dL  # noqa: E731
+    win, solo = KeyframeWindow(), KeyframeWindow()
+
+    def timed(fn):
+        for _ in range(2):
+            fn()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+              for _ in range(reps)]
+        dist.barrier()
+        torch.cuda.synchronize()
+        for a, b in ev:
+            flush.zero_()
+            a.record()
+            fn()
+            b.record()
+        dist.barrier()
+        torch.cuda.synchronize()
+        tt = torch.tensor([sum(a.elapsed_time(b) for a, b in ev) / reps], device=dev,
+                          dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt[0])
+
+    t_g = timed(lambda: win.gradients(params, cams, up, check=False))
+    win.exchange_check()
+    got = win.gradients(params, cams, up).clone()
+    t_1 = timed(lambda: solo.accumulate(params, cams, up, local_only=True))
+    want = solo.accumulate(params, cams, up, local_only=True)[0]
+    rel = torch.tensor([float((got.double() - want.double()).norm() / want.double().norm())],
+                       device=dev, dtype=torch.float64)
+    dist.all_reduce(rel, op=dist.ReduceOp.MAX)
+    del win, solo
+    return {"config": f"{cfg}: {H}x{W}, {params[0].shape[0]} surfels, {K}-keyframe window "
+                      f"sharded over {world} GPUs (keyframe k on rank k mod {world})",
+            "keyframes": K, "ms_per_window": t_g, "keyframes_per_s": K * 1e3 / t_g,
+            "ms_per_window_1gpu": t_1, "of_linear": t_1 / (world * t_g),
+            "rel_err_vs_1gpu": float(rel[0])}
 
 
 def adam_stage(P, dev, iters=50):
@@ -524,27 +682,33 @@ def cpu_baseline(cfg, full=True):
 
 
 def run_reference(args, rank, world, local_rank):
-    """The UNMODIFIED reference CUDA rasterizer (oracle/_ref, built from /root/reference by
-    oracle/Makefile) on the same frames.  The reference has no CPU implementation of this path;
-    its CUDA build is what BASELINE.json's target (>= 3x) is quoted against, so that is what
-    this arm times, with the CPU oracle port reported beside it."""
-    if rank != 0:
-        return None
+    """The UNMODIFIED reference CUDA rasterizer (oracle/_ref: the reference's .cu sources
+    compiled where they lie + oracle/ref_shim.cu, a lean extern "C" wrapper) on the same frames.
+    The reference has no CPU implementation of this path; its CUDA build is what BASELINE.json's
+    target (>= 3x) is quoted against, so that is what this arm times, with the CPU oracle port
+    reported beside it.  At N > 1 every rank runs the reference on its own GPU and keyframe (N
+    independent replicas - the reference has no multi-GPU form and no gradient sum), value =
+    N frames per slowest rank's step."""
     import reflib
     line = {"impl": "reference", "metric": METRIC, "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic"}
     if not reflib.available():
+        if rank != 0:
+            return None
         cb = cpu_baseline(args.config)
+        H, W, _, P, _ = scenes.CONFIGS[args.config]
         line.update(value=cb["value"], ms_per_step=1e3 / cb["value"], cpu_baseline=cb,
-                    config={"workload": f"{args.config} on the CPU oracle port (reference CUDA "
-                                        "build oracle/_ref or GPU not available)"},
+                    config={"workload": workload(args.config, H, W, P),
+                            "implementation": "CPU oracle port (the reference CUDA build "
+                                              "oracle/_ref or a GPU is not available)"},
                     e2e={"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0,
                          "d2h_bytes_per_step": 0})
         return line
+    import torch.distributed as dist
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
-    t = scene_tensors(args.config, 0, dev)
+    t = scene_tensors(args.config, rank, dev)
     H, W, P = t["H"], t["W"], t["means3D"].shape[0]
     opa = t["opacities"].reshape(-1).contiguous()
     ref = reflib.RefRasterizer()
@@ -556,44 +720,61 @@ def run_reference(args, rank, world, local_rank):
         g = ref.backward(x["dL_dout"], sync=False)
         return R, out, g
 
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
     for _ in range(max(args.warmup, 3)):
         frame(t, opa)
     torch.cuda.synchronize()
 
-    def timed(fn):
-        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-              for _ in range(args.steps)]
-        torch.cuda.synchronize()
-        for a, b in ev:
-            flush.zero_()
-            a.record()
-            fn()
-            b.record()
-            b.synchronize()
-        torch.cuda.synchronize()
-        return sum(a.elapsed_time(b) for a, b in ev) / args.steps
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    total_ms = timed_steps(lambda: frame(t, opa), args.steps, flush, barrier)
+    clocks = sampler.stop() if sampler else None
+    hp = scene_tensors(args.config, rank, dev, pinned=True)
+    keys = PARAM_KEYS + ("dL_dout",)
+    d_in = []
+    for b in range(2):
+        d = {k: torch.empty_like(hp[k], device=dev) for k in keys}
+        d["viewmatrix"], d["projmatrix"] = t["viewmatrix"], t["projmatrix"]
+        d_in.append(d)
 
-    sampler = ClockSampler(local_rank)
-    ms = timed(lambda: frame(t, opa))
-    line["clocks"] = sampler.stop()
-    hp = scene_tensors(args.config, 0, dev, pinned=True)
-    keys = ("means3D", "opacities", "scales", "rotations", "dL_dout")
+    def copy_in(b):
+        for k in keys:
+            d_in[b][k].copy_(hp[k], non_blocking=True)
 
-    def e2e_frame(x, slot):
+    def e2e_frame(b):
+        x = d_in[b]
         R, out, g = frame(x, x["opacities"].reshape(-1))
         return [out, g["means3D"], g["opacity"], g["scales"], g["rotations"]]
 
-    ms_e2e, h2d, d2h = pipelined_e2e(dev, hp, keys, args.steps, flush, e2e_frame,
-                                     [(7, H, W), (P, 3), (P, 1), (P, 2), (P, 4)])
+    barrier()
+    ms_e2e, d2h = pipelined_e2e(dev, args.steps, flush, copy_in, e2e_frame,
+                                [(7, H, W), (P, 3), (P, 1), (P, 2), (P, 4)])
+    barrier()
+    e2e_ms = ms_e2e * args.steps
+    if world > 1:
+        tt = torch.tensor([total_ms, e2e_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        total_ms, e2e_ms = float(tt[0]), float(tt[1])
+    if rank != 0:
+        return None
+    ms = total_ms / args.steps
     line.update(
-        value=1e3 / ms, ms_per_step=ms,
-        config={"workload": f"{args.config}: {H}x{W}, {P} surfels, fwd+bwd per frame, UNMODIFIED "
-                            "reference CUDA rasterizer (oracle/_ref), 1 GPU",
-                "l2": "192 MB buffer (1.5x the 126 MB L2) written between timed steps"},
+        value=world * 1e3 / ms, ms_per_step=ms, clocks=clocks,
+        config={"workload": workload(args.config, H, W, P),
+                "implementation": "UNMODIFIED reference CUDA rasterizer: its .cu sources compiled "
+                                  "where they lie + oracle/ref_shim.cu (oracle/_ref), not the "
+                                  "torch binding of its setup.py",
+                "exchange": "none (the reference is single-GPU: N independent replicas)"
+                if world > 1 else "none (one GPU)",
+                "l2": L2_NOTE, "parallelism": f"{world} independent replicas"},
         kind="reference",
-        e2e={"value": 1e3 / ms_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d,
-             "d2h_bytes_per_step": d2h})
-    if not args.no_cpu_baseline:
+        e2e={"value": world * 1e3 / (e2e_ms / args.steps), "unit": UNIT,
+             "h2d_bytes_per_step": sum(hp[k].numel() * 4 for k in keys) * world,
+             "d2h_bytes_per_step": d2h * world})
+    if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args.config)
     return line
 
@@ -606,25 +787,24 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="C2", choices=list(scenes.CONFIGS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-window", action="store_true",
+                    help="N>1: skip the C3 / C4 keyframe-window measurement")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if args.impl == "reference":
-        line = run_reference(args, rank, world, local_rank)
-        if line is not None:
-            print(json.dumps(line), flush=True)
-        return
-    if not torch.cuda.is_available():
+    if args.impl == "ours" and not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
-    if world > 1:
+    if world > 1 and torch.cuda.is_available():
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", rank=rank, world_size=world,
                                 device_id=torch.device("cuda", local_rank))
-    line = run_ours(args, rank, world, local_rank)
-    if world > 1:
+    elif world > 1 and rank != 0:
+        return
+    line = (run_reference if args.impl == "reference" else run_ours)(args, rank, world, local_rank)
+    if world > 1 and torch.cuda.is_available():
         import torch.distributed as dist
         dist.barrier()
         dist.destroy_process_group()

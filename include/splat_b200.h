@@ -274,11 +274,16 @@ SPLAT_API int sknn_dist2_static(int P, const float *points, float *mean_dists, v
  * after which splat_xchg_result(x) - a [P,10] device array owned by the exchange - holds the
  * sum over ranks, bit-identical on every rank (each row is summed once, by its owner, in
  * rank order).  Work is ordered by `stream`; the kernels wait for peers through flags in
- * peer memory and give up after ~2 s (reported by the next splat_xchg_* call).  All ranks
- * must make the same sequence of calls.  world <= 16; peers must be NVLink/P2P reachable.
+ * peer memory.  A wait gives up after 30 s (SPLAT_B200_XCHG_TIMEOUT_MS overrides, read by
+ * splat_xchg_create); the rank that gave up marks EVERY rank's arena before it goes on, so
+ * by the end of the same exchange every rank holds the fault: splat_xchg_fault() returns
+ * non-zero once the stream has been synchronised, and every later splat_xchg_* call fails.
+ * The sums of a faulted exchange contain stale rows - do not apply them; destroy and
+ * re-create the exchange.  All ranks must make the same sequence of calls.  world <= 16;
+ * peers must be NVLink/P2P reachable.
  * splat_xchg_connect_local wires exchanges that live in ONE process (tests, or a process
- * driving several GPUs); with it, when several ranks share a stream, issue every rank's
- * reduce before any rank's wait. */
+ * driving several GPUs; it enables peer access between the devices involved); with it, when
+ * several ranks share a stream, issue every rank's reduce before any rank's wait. */
 #define SPLAT_XCHG_HANDLE_BYTES 64
 typedef struct splat_xchg splat_xchg;
 SPLAT_API int splat_xchg_create(int P, int world, int rank, splat_xchg **out);
@@ -290,6 +295,9 @@ SPLAT_API int splat_xchg_reduce(splat_xchg *x, void *stream);
 SPLAT_API int splat_xchg_wait(splat_xchg *x, void *stream);
 SPLAT_API int splat_xchg_allreduce(splat_xchg *x, void *stream);
 SPLAT_API float *splat_xchg_result(splat_xchg *x);
+/* 0, or the fault code (1 + step + 16 * rank waited for) a wait of this or a peer rank left
+ * behind.  Reads a host word: synchronise the stream of the last allreduce first. */
+SPLAT_API int splat_xchg_fault(splat_xchg *x);
 SPLAT_API int splat_xchg_destroy(splat_xchg *x);
 
 /* ---- per-stage device timing ----------------------------------------------------
@@ -305,6 +313,11 @@ SPLAT_API int splat_xchg_destroy(splat_xchg *x);
 SPLAT_API int splat_profile_enable(int on);
 SPLAT_API int splat_profile_select(const char *stage);
 SPLAT_API int splat_profile_read(int max_stages, const char **names, float *ms);
+
+/* Number of kernels this library has launched so far in this process (all threads, all
+ * devices).  No counterpart in the reference.  A harness takes the difference around a timed
+ * region to report how many of the library's kernels ran in it. */
+SPLAT_API unsigned long long splat_launch_count(void);
 
 SPLAT_API const char *splat_last_error(void);
 SPLAT_API int splat_abi_version(void);

@@ -173,7 +173,7 @@ extern "C" int splat_activation_adam_step(const splat_adam_args *x) {
   a.scaling_max = (float)x->scaling_max;
   a.scaling_penalty = (float)x->scaling_max_penalty;
   a.reg_out = x->reg_out;
-  activation_adam_kernel<<<(x->P + 255) / 256, 256, 0, (cudaStream_t)x->stream>>>(a);
+  activation_adam_kernel<<<(x->P + 255) / 256, 256, 0, LS((cudaStream_t)x->stream)>>>(a);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : splat_fail("splat_activation_adam_step: %s", cudaGetErrorString(e));
 }

@@ -296,6 +296,15 @@ unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long
                                        int unpack_last, int idx_bits, uint32_t n_estimate,
                                        cudaStream_t s, const MaskParams *mp = nullptr,
                                        uint32_t P = 0);
+// Number of SMs of the current device (queried once per device, then cached): grids of
+// persistent / grid-stride kernels are sized from it.
+int splat_sm_count();
+// Every kernel launch of the library is counted (splat_launch_count() reads the total), so a
+// harness can report how many of OUR kernels ran inside a timed region.
+void splat_count_launch(int n = 1);
+// LS(stream): the stream argument of a <<<>>> launch, counting the launch on the way
+#define LS(s) (splat_count_launch(1), (s))
+
 // Function attributes (opt-in shared memory, carve-out) are per device: true the first time a
 // call site runs on the current device (one bit per device in the caller's static mask).
 static inline bool first_use_on_device(unsigned long long &seen) {
@@ -306,7 +315,11 @@ static inline bool first_use_on_device(unsigned long long &seen) {
   seen |= bit;
   return true;
 }
-void launch_bwd_order(const ImageView &im, void *fill, size_t fill_bytes, cudaStream_t s);
+struct FillList {           // float arrays to clear (any 4-byte alignment, any placement)
+  float *ptr[4];
+  size_t n[4];
+};
+void launch_bwd_order(const ImageView &im, const FillList &fill, cudaStream_t s);
 void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageView &im,
                            const BinView &b, uint32_t capacity, cudaStream_t s);
 

@@ -3,6 +3,7 @@
 // CudaRasterizer::Rasterizer::forward / backward / markVisible
 // (submodules/diff-surfel-spherical-rasterization/cuda_rasterizer/rasterizer_impl.cu:
 // 117-122, 170-262, 266-313).
+#include <atomic>
 #include <chrono>
 #include <cstdarg>
 #include <cstdlib>
@@ -18,10 +19,17 @@ static thread_local std::string g_err;
 
 namespace {
 
-thread_local uint32_t *g_pinned = nullptr;      // 2 words: num_rendered, status (mapped)
-thread_local uint32_t *g_pinned_dev = nullptr;  // the device's view of g_pinned
-thread_local cudaEvent_t g_event = nullptr;
-thread_local uint32_t g_last_count = 0;         // num_rendered of this thread's previous forward
+// Host-side state of dssr_forward, per host thread AND per device: a thread that drives
+// several GPUs gets an event (events belong to the device they were created on), a count word
+// and a size estimate for each of them.
+constexpr int MAX_DEVICES = 64;
+struct DeviceState {
+  uint32_t *pinned = nullptr;      // 2 words: num_rendered, status (mapped pinned host memory)
+  uint32_t *pinned_dev = nullptr;  // this device's view of `pinned`
+  cudaEvent_t event = nullptr;     // "the count has landed"
+  uint32_t last_count = 0;         // num_rendered of the previous forward on this device
+};
+thread_local DeviceState g_state[MAX_DEVICES];
 
 #define fail splat_fail
 
@@ -63,6 +71,7 @@ struct Prof {
   struct Rec {
     const char *name;
     cudaEvent_t beg, end;
+    int dev;               // the device the two events were created on
   };
   bool on = false;
   std::string only;        // empty: every stage
@@ -70,8 +79,21 @@ struct Prof {
   size_t used = 0;
   Rec *take(const char *nm) {
     if (!on || (!only.empty() && only != nm)) return nullptr;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (used < pool.size() && pool[used].dev != dev) {   // pooled events of another device
+      cudaEventDestroy(pool[used].beg);
+      cudaEventDestroy(pool[used].end);
+      pool[used].beg = pool[used].end = nullptr;
+      if (cudaEventCreate(&pool[used].beg) != cudaSuccess ||
+          cudaEventCreate(&pool[used].end) != cudaSuccess) {
+        pool.resize(used);   // (later entries are recreated on demand)
+        return nullptr;
+      }
+      pool[used].dev = dev;
+    }
     if (used == pool.size()) {
-      Rec r{nm, nullptr, nullptr};
+      Rec r{nm, nullptr, nullptr, dev};
       if (cudaEventCreate(&r.beg) != cudaSuccess) return nullptr;
       if (cudaEventCreate(&r.end) != cudaSuccess) {
         cudaEventDestroy(r.beg);
@@ -97,14 +119,21 @@ struct ProfScope {
   }
 };
 
-int ensure_host_scratch() {
-  if (!g_pinned) {
-    CUDA_TRY(cudaHostAlloc((void **)&g_pinned, 64, cudaHostAllocPortable | cudaHostAllocMapped));
-    CUDA_TRY(cudaHostGetDevicePointer((void **)&g_pinned_dev, g_pinned, 0));
+int device_state(DeviceState **out) {
+  int dev = 0;
+  CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= MAX_DEVICES) return fail("device ordinal %d out of range", dev);
+  DeviceState &d = g_state[dev];
+  if (!d.pinned) {
+    CUDA_TRY(cudaHostAlloc((void **)&d.pinned, 64, cudaHostAllocPortable | cudaHostAllocMapped));
+    CUDA_TRY(cudaHostGetDevicePointer((void **)&d.pinned_dev, d.pinned, 0));
   }
-  if (!g_event) CUDA_TRY(cudaEventCreateWithFlags(&g_event, cudaEventDisableTiming));
+  if (!d.event) CUDA_TRY(cudaEventCreateWithFlags(&d.event, cudaEventDisableTiming));
+  *out = &d;
   return 0;
 }
+
+std::atomic<unsigned long long> g_launches{0};
 
 int run_binning_and_render(const dssr_forward_args *a, const FwdParams &fp,
                            const GeomView &gv, const ImageView &iv, const SortPlan &sp,
@@ -136,6 +165,22 @@ int run_binning_and_render(const dssr_forward_args *a, const FwdParams &fp,
 
 }  // namespace
 
+void splat_count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+
+int splat_sm_count() {
+  static std::atomic<int> cache[MAX_DEVICES];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= MAX_DEVICES) dev = 0;
+  int n = cache[dev].load(std::memory_order_relaxed);
+  if (n <= 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n < 1)
+      n = 1;
+    cache[dev].store(n, std::memory_order_relaxed);
+  }
+  return n;
+}
+
 int splat_fail(const char *fmt, ...) {
   char buf[512];
   va_list ap;
@@ -149,7 +194,8 @@ int splat_fail(const char *fmt, ...) {
 extern "C" {
 
 const char *splat_last_error(void) { return g_err.c_str(); }
-int splat_abi_version(void) { return 7; }
+int splat_abi_version(void) { return 8; }
+unsigned long long splat_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 size_t dssr_geometry_bytes(int P) { return GeomLayout(P < 0 ? 0 : P).total; }
 size_t dssr_image_bytes(int W, int H) { return ImageLayout(W, H).total; }
@@ -212,7 +258,8 @@ int dssr_forward(const dssr_forward_args *a, int *num_rendered) {
       ((uintptr_t)a->transMat_precomp & 15))
     return fail("dssr_forward: scales must be 8-byte and rotations / transMat_precomp 16-byte aligned");
   Trace tr;
-  if (ensure_host_scratch()) return 1;
+  DeviceState *ds = nullptr;
+  if (device_state(&ds)) return 1;
   const bool dbg = a->debug & 1;
 
   GeomLayout gl(a->P);
@@ -241,10 +288,10 @@ int dssr_forward(const dssr_forward_args *a, int *num_rendered) {
   {
     ProfScope ps("preprocess", st);
     launch_preprocess(fp, gv, iv, st);
-    launch_chunk_scan(gv, g_pinned_dev, st);   // count + status land in g_pinned
+    launch_chunk_scan(gv, ds->pinned_dev, st);   // count + status land in ds->pinned
   }
   LAUNCH_CHECK(dbg, st, "preprocess");
-  CUDA_TRY(cudaEventRecord(g_event, st));
+  CUDA_TRY(cudaEventRecord(ds->event, st));
   tr.lap("enqueue preprocess");
 
   // With a capacity hint the rest of the frame is enqueued BEFORE the host waits for
@@ -255,16 +302,17 @@ int dssr_forward(const dssr_forward_args *a, int *num_rendered) {
   // count of this thread when that fits the hint, else the hint itself)
   if (hint > 0)
     if (run_binning_and_render(a, fp, gv, iv, sp, (uint32_t)hint,
-                               g_last_count && g_last_count <= hint ? g_last_count : (uint32_t)hint, st))
+                               ds->last_count && ds->last_count <= hint ? ds->last_count
+                                                                          : (uint32_t)hint, st))
       return 1;
   tr.lap("enqueue binning (hint)");
-  CUDA_TRY(cudaEventSynchronize(g_event));
+  CUDA_TRY(cudaEventSynchronize(ds->event));
   tr.lap("wait for count");
-  const uint32_t N = g_pinned[0], status = g_pinned[1];
+  const uint32_t N = ds->pinned[0], status = ds->pinned[1];
   if (status & 1u)
     return fail("Point is filtered although prefiltered is set. This shouldn't happen!");
   if (N > 0x3fffffffu) return fail("dssr_forward: %u instances exceed the 2^30 limit", N);
-  g_last_count = N;
+  ds->last_count = N;
   if (hint <= 0 || (int64_t)N > hint)
     if (run_binning_and_render(a, fp, gv, iv, sp, N, N, st)) return 1;
   tr.lap("enqueue binning (exact)");
@@ -290,32 +338,13 @@ int dssr_backward(const dssr_backward_args *a) {
     return fail("dssr_backward: scales / dL_dscales must be 8-byte and rotations / "
                 "dL_drotations / dL_dtransMat 16-byte aligned");
   const bool dbg = a->debug & 1;
-  char *fused_fill = nullptr;
-  size_t fused_bytes = 0;
-  {
-    // the four accumulation targets must start at zero; when the caller laid them out back to
-    // back (as _C.py does, one allocation) that is ONE fill instead of four
-    char *ptr[4] = {(char *)a->dL_dmeans2D, (char *)a->dL_dnormal, (char *)a->dL_dopacity,
-                    (char *)a->dL_dtransMat};
-    const size_t len[4] = {12 * P, 12 * P, 4 * P, 48 * P};
-    char *lo = ptr[0], *hi = ptr[0] + len[0];
-    for (int i = 1; i < 4; i++) {
-      if (ptr[i] < lo) lo = ptr[i];
-      if (ptr[i] + len[i] > hi) hi = ptr[i] + len[i];
-    }
-    if ((size_t)(hi - lo) <= 76 * P + 4096) {
-      if (((uintptr_t)lo & 15) == 0) {   // zeroed by the work-order launch below
-        fused_fill = lo;
-        fused_bytes = (size_t)(hi - lo) & ~(size_t)15;
-        if (fused_bytes != (size_t)(hi - lo))
-          CUDA_TRY(cudaMemsetAsync(lo + fused_bytes, 0, (size_t)(hi - lo) - fused_bytes, st));
-      } else {
-        CUDA_TRY(cudaMemsetAsync(lo, 0, (size_t)(hi - lo), st));
-      }
-    } else {
-      for (int i = 0; i < 4; i++) CUDA_TRY(cudaMemsetAsync(ptr[i], 0, len[i], st));
-    }
-  }
+  // The four accumulation targets must start at zero: they are cleared - exactly these four
+  // arrays, wherever the caller put them - by spare blocks of the work-order launch below.
+  FillList fill;
+  fill.ptr[0] = a->dL_dmeans2D;  fill.n[0] = 3 * P;
+  fill.ptr[1] = a->dL_dnormal;   fill.n[1] = 3 * P;
+  fill.ptr[2] = a->dL_dopacity;  fill.n[2] = P;
+  fill.ptr[3] = a->dL_dtransMat; fill.n[3] = 12 * P;
   ImageLayout il(a->W, a->H);
   SortPlan sp(a->P, il.tiles);
   GeomView gv = make_geom_view(a->geom_buffer, a->P);
@@ -341,7 +370,7 @@ int dssr_backward(const dssr_backward_args *a) {
   {
     ProfScope ps("render_backward", st);
     // here, not in the forward: forward-only renders do not pay for it
-    launch_bwd_order(iv, fused_fill, fused_bytes, st);
+    launch_bwd_order(iv, fill, st);
     launch_render_backward(bp, gv, iv, bv, st);
   }
   LAUNCH_CHECK(dbg, st, "render_backward");

@@ -454,19 +454,19 @@ backward_preprocess_kernel(int P, const int *__restrict__ radii,
 
 void launch_render_backward(const BwdParams &p, const GeomView &g, const ImageView &im,
                             const BinView &b, cudaStream_t s) {
-  render_backward_kernel<<<im.tiles * SUBS_PER_TILE, 32, 0, s>>>(
+  render_backward_kernel<<<im.tiles * SUBS_PER_TILE, 32, 0, LS(s)>>>(
       im.ranges, im.bwd_order, b.point_list, reinterpret_cast<const uint16_t *>(b.hdr), b.hdr, g.rec,
       p.projmatrix, p.W, p.H, im.tiles_x, (uint32_t)p.P, im.final_T, im.n_contrib, p.dL_dout, p.dL_dtransMat, p.dL_dnormal, p.dL_dopacity);
 }
 
 void launch_backward_preprocess(const BwdParams &p, cudaStream_t s) {
   if (p.push)
-    backward_preprocess_kernel<true><<<(p.P + 255) / 256, 256, 0, s>>>(
+    backward_preprocess_kernel<true><<<(p.P + 255) / 256, 256, 0, LS(s)>>>(
         p.P, p.radii, p.scales, p.rotations, p.viewmatrix, p.dL_dtransMat, p.dL_dnormal,
         p.dL_dopacity, p.dL_dmeans3D, p.dL_dscales, p.dL_drotations, p.packed,
         p.packed_accumulate, *p.push);
   else
-    backward_preprocess_kernel<false><<<(p.P + 255) / 256, 256, 0, s>>>(
+    backward_preprocess_kernel<false><<<(p.P + 255) / 256, 256, 0, LS(s)>>>(
         p.P, p.radii, p.scales, p.rotations, p.viewmatrix, p.dL_dtransMat, p.dL_dnormal,
         p.dL_dopacity, p.dL_dmeans3D, p.dL_dscales, p.dL_drotations, p.packed,
         p.packed_accumulate, XchgView());

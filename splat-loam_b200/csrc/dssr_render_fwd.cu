@@ -254,17 +254,30 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
 // the number of entries they walk (correlation 0.85, against 0.35 for the tile's list length),
 // so longest-first numbering packs the waves: list scheduling of the measured warp times gave
 // 363 us against 618 us for the tile-length order.
-// Blocks 1.. of the same launch zero the backward's accumulation buffers (`fill`, n16 16-byte
-// words) meanwhile: one launch instead of a fill and a kernel one after the other.
+// Blocks 1.. of the same launch zero the backward's accumulation buffers (`fill`: four float
+// arrays) meanwhile: one launch instead of fills and a kernel one after the other.
 constexpr int COST_BINS = 2048;
 __global__ void __launch_bounds__(1024)
 bwd_order_kernel(const uint32_t *__restrict__ sub_cost, int units, uint32_t *__restrict__ order,
-                 float4 *__restrict__ fill, size_t n16) {
+                 FillList fill) {
   if (blockIdx.x > 0) {
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (size_t k = (size_t)(blockIdx.x - 1) * 1024 + threadIdx.x; k < n16;
-         k += (size_t)(gridDim.x - 1) * 1024)
-      fill[k] = z;
+    const size_t t0 = (size_t)(blockIdx.x - 1) * 1024 + threadIdx.x;
+    const size_t stride = (size_t)(gridDim.x - 1) * 1024;
+#pragma unroll
+    for (int a = 0; a < 4; a++) {
+      float *p = fill.ptr[a];
+      const size_t n = fill.n[a];
+      // scalar head up to the first 16-byte boundary, float4 body, scalar tail
+      size_t head = ((16u - ((uintptr_t)p & 15u)) & 15u) / 4u;
+      if (head > n) head = n;
+      const size_t body = (n - head) / 4;
+      float4 *p4 = reinterpret_cast<float4 *>(p + head);
+      for (size_t k = t0; k < body; k += stride) p4[k] = z;
+      if (t0 < head) p[t0] = 0.f;
+      const size_t tail0 = head + 4 * body;
+      if (t0 < n - tail0) p[tail0 + t0] = 0.f;
+    }
     return;
   }
   __shared__ uint32_t s_bin[COST_BINS];
@@ -298,11 +311,9 @@ bwd_order_kernel(const uint32_t *__restrict__ sub_cost, int units, uint32_t *__r
 
 }  // namespace
 
-// `fill` (16-byte aligned, fill_bytes a multiple of 16) is zeroed by the same launch; nullptr: no fill
-void launch_bwd_order(const ImageView &im, void *fill, size_t fill_bytes, cudaStream_t s) {
-  const int fill_blocks = fill ? 296 : 0;
-  bwd_order_kernel<<<1 + fill_blocks, 1024, 0, s>>>(im.sub_cost, im.tiles * SUBS_PER_TILE,
-                                                    im.bwd_order, (float4 *)fill, fill_bytes / 16);
+void launch_bwd_order(const ImageView &im, const FillList &fill, cudaStream_t s) {
+  bwd_order_kernel<<<1 + 2 * splat_sm_count(), 1024, 0, LS(s)>>>(
+      im.sub_cost, im.tiles * SUBS_PER_TILE, im.bwd_order, fill);
 }
 
 void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageView &im,
@@ -312,7 +323,7 @@ void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageVie
   if (first_use_on_device(seen))   // one-warp CTAs: residency is limited by the carve-out
     cudaFuncSetAttribute(render_forward_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                          cudaSharedmemCarveoutMaxShared);
-  render_forward_kernel<<<im.tiles * SUBS_PER_TILE, 32, 0, s>>>(
+  render_forward_kernel<<<im.tiles * SUBS_PER_TILE, 32, 0, LS(s)>>>(
       im.ranges, order, b.point_list, b.sub_mask, g.rec, p.projmatrix, p.W, p.H, im.tiles_x,
       capacity, (uint32_t)p.P, im.final_T, im.n_contrib, p.out_maps, im.sub_cost);
 }

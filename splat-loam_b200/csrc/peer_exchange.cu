@@ -3,6 +3,7 @@
 // executed by the per-surfel VJP kernel itself (dssr_render_bwd.cu), so the transfer of a
 // row starts the moment it has been computed.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "../../include/splat_b200.h"
@@ -83,11 +84,17 @@ __global__ void __launch_bounds__(256) xchg_reduce_kernel(XchgView x) {
   if (DRAIN) {
     if (threadIdx.x == 0) s_last = last;
     __syncthreads();
-    if (s_last) xchg_await(x, 1);
+    if (s_last) {
+      xchg_await(x, 1);
+      if (threadIdx.x == 0) xchg_collect_fault(x);
+    }
   }
 }
 
-__global__ void __launch_bounds__(32) xchg_wait_kernel(XchgView x) { xchg_await(x, 1); }
+__global__ void __launch_bounds__(32) xchg_wait_kernel(XchgView x) {
+  xchg_await(x, 1);
+  if (threadIdx.x == 0) xchg_collect_fault(x);
+}
 
 int xfail(const char *msg, cudaError_t e = cudaSuccess) {
   if (e != cudaSuccess) return splat_fail("%s: %s", msg, cudaGetErrorString(e));
@@ -98,24 +105,27 @@ int xfail(const char *msg, cudaError_t e = cudaSuccess) {
 
 void launch_xchg_push(const XchgView &x, const float *src, int P, cudaStream_t s) {
   const int blocks = (P + XCHG_SLICE_ALIGN - 1) / XCHG_SLICE_ALIGN;
-  xchg_push_kernel<<<blocks < 148 * 8 ? blocks : 148 * 8, 256, 0, s>>>(x, src, P);
+  const int cap = splat_sm_count() * 8;
+  xchg_push_kernel<<<blocks < cap ? blocks : cap, 256, 0, LS(s)>>>(x, src, P);
 }
 void launch_xchg_reduce(const XchgView &x, bool drain, cudaStream_t s) {
+  const int sms = splat_sm_count();
   if (drain)
-    xchg_reduce_kernel<true><<<148, 256, 0, s>>>(x);
+    xchg_reduce_kernel<true><<<sms, 256, 0, LS(s)>>>(x);
   else
-    xchg_reduce_kernel<false><<<148, 256, 0, s>>>(x);
+    xchg_reduce_kernel<false><<<sms, 256, 0, LS(s)>>>(x);
 }
 void launch_xchg_wait(const XchgView &x, cudaStream_t s) {
-  xchg_wait_kernel<<<1, 32, 0, s>>>(x);
+  xchg_wait_kernel<<<1, 32, 0, LS(s)>>>(x);
 }
 
 static int xchg_ready(splat_xchg *x, const char *who) {
   if (!x) return splat_fail("%s: NULL exchange", who);
   if (!x->connected) return splat_fail("%s: exchange is not connected", who);
   if (*x->fault_host)
-    return splat_fail("%s: an earlier exchange gave up waiting for a peer (step %u)", who,
-                      *x->fault_host - 1u);
+    return splat_fail("%s: an earlier exchange gave up waiting for rank %u (step %u) - its sums "
+                      "are invalid on every rank; destroy and re-create the exchange", who,
+                      (*x->fault_host - 1u) / 16u, (*x->fault_host - 1u) % 16u);
   return 0;
 }
 
@@ -147,6 +157,11 @@ int splat_xchg_create(int P, int world, int rank, splat_xchg **out) {
   int rows = (P + world - 1) / world;
   x->v.slice_rows = (rows + XCHG_SLICE_ALIGN - 1) / XCHG_SLICE_ALIGN * XCHG_SLICE_ALIGN;
   x->v.epoch = 0;
+  x->v.timeout_ns = XCHG_DEFAULT_TIMEOUT_NS;
+  if (const char *t = getenv("SPLAT_B200_XCHG_TIMEOUT_MS")) {
+    const double ms = atof(t);
+    if (ms > 0) x->v.timeout_ns = (unsigned long long)(ms * 1e6);
+  }
   x->arena_bytes = 256 + 2 * x->v.stage_bytes();
   cudaError_t e = cudaGetDevice(&x->device);
   if (e == cudaSuccess) e = cudaMalloc((void **)&x->own, x->arena_bytes);
@@ -205,6 +220,19 @@ int splat_xchg_connect_local(splat_xchg *x, splat_xchg *const *peers) {
         peers[r]->P != x->P)
       return xfail("splat_xchg_connect_local: peers do not form one window");
     x->v.arena[r] = peers[r]->own;
+    if (peers[r]->device != x->device) {   // kernels on our device store into the peer's arena
+      int cur = 0, can = 0;
+      cudaGetDevice(&cur);
+      cudaDeviceCanAccessPeer(&can, x->device, peers[r]->device);
+      if (!can)
+        return splat_fail("splat_xchg_connect_local: device %d cannot access device %d",
+                          x->device, peers[r]->device);
+      cudaSetDevice(x->device);
+      cudaError_t e = cudaDeviceEnablePeerAccess(peers[r]->device, 0);
+      cudaSetDevice(cur);
+      if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+      else if (e != cudaSuccess) return xfail("splat_xchg_connect_local: cudaDeviceEnablePeerAccess", e);
+    }
   }
   x->local = x->v.world > 1;
   x->connected = true;
@@ -250,6 +278,11 @@ int splat_xchg_allreduce(splat_xchg *x, void *stream) {
   x->pushed = false;
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : xfail("splat_xchg_allreduce", e);
+}
+
+int splat_xchg_fault(splat_xchg *x) {
+  if (!x || !x->fault_host) return 0;
+  return (int)*x->fault_host;
 }
 
 float *splat_xchg_result(splat_xchg *x) {

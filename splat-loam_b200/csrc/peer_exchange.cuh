@@ -16,7 +16,8 @@
 #define XCHG_ROW 10             // floats per surfel: means3D 3 | opacity 1 | scales 2 | rotations 4
 #define XCHG_SLICE_ALIGN 256    // slice_rows is a multiple of this: a 256-row block of the push
                                 // kernels has ONE owner and a contiguous, 16-byte aligned target
-#define XCHG_SPIN_LIMIT (4ll * 1000 * 1000 * 1000)   // clock64 ticks (~2 s) before giving up
+#define XCHG_DEFAULT_TIMEOUT_NS (30ull * 1000 * 1000 * 1000)   // a wait gives up after this long
+                                // (%globaltimer nanoseconds; SPLAT_B200_XCHG_TIMEOUT_MS overrides)
 
 // Per-rank arena (one cudaMalloc, peer-mapped through CUDA IPC):
 //   [ flags u32[2][XCHG_MAX_WORLD] | ticket u32[2] | pad to 256 B |
@@ -24,13 +25,16 @@
 struct XchgArena {
   uint32_t flags[2][XCHG_MAX_WORLD];
   uint32_t ticket[2];
-  uint32_t pad[64 - 2 * XCHG_MAX_WORLD - 2];
+  uint32_t fault;     // set (by ANY rank, through peer memory) when a wait gave up: the sums of
+                      // this and every later epoch are not to be trusted
+  uint32_t pad[64 - 2 * XCHG_MAX_WORLD - 3];
 };
 static_assert(sizeof(XchgArena) == 256, "arena header is 256 bytes");
 
 struct XchgView {
   char *arena[XCHG_MAX_WORLD];   // every rank's arena as mapped in THIS process (own included)
   uint32_t *fault;               // mapped pinned host word: set when a wait gave up
+  unsigned long long timeout_ns; // how long a wait spins before it gives up
   int world, rank, slice_rows;
   uint32_t epoch;
 
@@ -87,15 +91,31 @@ __device__ __forceinline__ bool xchg_publish(const XchgView &x, int step) {
   return last;
 }
 
+__device__ __forceinline__ unsigned long long xchg_now_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
 // Block-wide: wait until every rank has published `epoch` for `step` (flags live in OUR arena).
 // Epochs only grow; wrap-around is handled by the signed difference.
+// A wait that gives up POISONS the exchange for everybody: the fault word of every rank's arena
+// is set through peer memory before this rank goes on (and publishes its own flags), so a peer
+// that later sees this rank's arrival also sees the fault (xchg_collect_fault).  The sums of a
+// poisoned epoch contain stale rows and must not be used.
 __device__ __forceinline__ void xchg_await(const XchgView &x, int step) {
   if (threadIdx.x < x.world) {
     volatile uint32_t *f = &x.hdr(x.rank)->flags[step][threadIdx.x];
-    const long long t0 = clock64();
+    const unsigned long long t0 = xchg_now_ns();
     while ((int32_t)(*f - x.epoch) < 0) {
-      if (clock64() - t0 > XCHG_SPIN_LIMIT) {
-        if (x.fault) *x.fault = 1u + (uint32_t)step;
+      if (xchg_now_ns() - t0 > x.timeout_ns) {
+        const uint32_t code = 1u + (uint32_t)step + 16u * (uint32_t)threadIdx.x;
+        for (int r = 0; r < x.world; r++) {
+          volatile uint32_t *pf = &x.hdr(r)->fault;
+          *pf = code;
+        }
+        __threadfence_system();
+        if (x.fault) *x.fault = code;
         break;
       }
       __nanosleep(100);
@@ -103,6 +123,14 @@ __device__ __forceinline__ void xchg_await(const XchgView &x, int step) {
   }
   __syncthreads();
   __threadfence_system();
+}
+
+// After the last wait of an exchange (one thread): hand a fault that any rank raised in our
+// arena to the host (mapped pinned word), where the next splat_xchg_* call and
+// splat_xchg_fault() find it.
+__device__ __forceinline__ void xchg_collect_fault(const XchgView &x) {
+  const uint32_t f = *(volatile uint32_t *)&x.hdr(x.rank)->fault;
+  if (f && x.fault) *x.fault = f;
 }
 
 struct splat_xchg;

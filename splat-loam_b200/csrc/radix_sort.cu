@@ -86,18 +86,24 @@ digit_scan_kernel(const uint32_t *__restrict__ hist, uint32_t *__restrict__ digi
 }
 
 // identifyTileRanges (rasterizer_impl.cu:94-114) for the > 1024 tiles case.
+// When the capacity hint was too small (*num_ptr > capacity) the passes above dropped words
+// and `keys` has holes of stale bytes: nothing is written then (ranges stay (0,0), the
+// compositing of this attempt is a no-op) and the frame is re-run with the exact size.  A tile
+// id beyond the grid can then never index `ranges`; the bound test stays as a second guard.
 __global__ void identify_ranges_kernel(const uint32_t *num_ptr, uint32_t capacity,
                                        const unsigned long long *__restrict__ keys,
-                                       uint2 *ranges) {
-  uint32_t L = min(*num_ptr, capacity);
+                                       uint2 *ranges, uint32_t tiles) {
+  if (*num_ptr > capacity) return;
+  uint32_t L = *num_ptr;
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= L) return;
   uint32_t cur = (uint32_t)(keys[i] >> 32);
+  if (cur >= tiles) return;
   if (i == 0) ranges[cur].x = 0;
   else {
     uint32_t prev = (uint32_t)(keys[i - 1] >> 32);
     if (cur != prev) {
-      ranges[prev].y = i;
+      if (prev < tiles) ranges[prev].y = i;
       ranges[cur].x = i;
     }
   }
@@ -449,7 +455,7 @@ extern "C" __attribute__((visibility("default"))) int splat_debug_sort_trace(uns
 void launch_digit_scan(const uint32_t *hist, uint32_t *digit_base, int npass, uint2 *ranges,
                        uint32_t *tile_order, int tiles, int tile_pass_single, int nrepl,
                        cudaStream_t s) {
-  digit_scan_kernel<<<npass, SORT_MAX_BINS, 0, s>>>(hist, digit_base, ranges, tile_order, tiles,
+  digit_scan_kernel<<<npass, SORT_MAX_BINS, 0, LS(s)>>>(hist, digit_base, ranges, tile_order, tiles,
                                                     tile_pass_single, nrepl);
 }
 
@@ -458,13 +464,7 @@ void launch_digit_scan(const uint32_t *hist, uint32_t *digit_base, int npass, ui
 // keys per thread are two waves, the second a third full; 287 CTAs of 12 are two full, shorter
 // ones.  `n_estimate`: the expected number of words (the capacity may be a generous hint).
 static int pick_items(uint32_t n_estimate) {
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1)
-      sms = 148;
-  }
+  const int sms = splat_sm_count();
   const int choices[3] = {16, 12, 8};
   int best = 16;
   long long best_cost = -1;
@@ -500,11 +500,11 @@ static void launch_one_pass(bool last, const unsigned long long *src, unsigned l
   if (nblk < 1) return;
   if (last)
     sort_last_pass_kernel<ITEMS><<<nblk, SORT_THREADS,
-                                   smem + (size_t)nbins * 4 + (size_t)SORT_THREADS * ITEMS * 8, s>>>(
+                                   smem + (size_t)nbins * 4 + (size_t)SORT_THREADS * ITEMS * 8, LS(s)>>>(
         src, keys_out, plist_out, mp, P, num_ptr, capacity, status, ticket, digit_base, shift, bits,
         idx_bits);
   else
-    sort_pass_kernel<ITEMS><<<nblk, SORT_THREADS, smem, s>>>(src, dst, num_ptr, capacity, status,
+    sort_pass_kernel<ITEMS><<<nblk, SORT_THREADS, smem, LS(s)>>>(src, dst, num_ptr, capacity, status,
                                                              ticket, digit_base, shift, bits);
 }
 
@@ -558,9 +558,9 @@ void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, con
     cudaMemsetAsync(im.ranges, 0, (size_t)im.tiles * sizeof(uint2), s);
     uint32_t blocks = (capacity + 255) / 256;
     if (blocks)
-      identify_ranges_kernel<<<blocks, 256, 0, s>>>(&g.hdr->num_rendered, capacity, b.keys,
-                                                    im.ranges);
+      identify_ranges_kernel<<<blocks, 256, 0, LS(s)>>>(&g.hdr->num_rendered, capacity, b.keys,
+                                                    im.ranges, (uint32_t)im.tiles);
   }
   if (single < 0 && im.tiles <= SPLAT_MAX_ORDERED_TILES)   // beyond that: identity order
-    tile_order_kernel<<<(im.tiles + 127) / 128, 128, 0, s>>>(im.ranges, im.tiles, im.tile_order);
+    tile_order_kernel<<<(im.tiles + 127) / 128, 128, 0, LS(s)>>>(im.ranges, im.tiles, im.tile_order);
 }

@@ -384,7 +384,7 @@ int dssr_post_forward(const dssr_post_forward_args *a) {
       !a->surf_normal)
     return splat_fail("dssr_post_forward: NULL pointer");
   dim3 grid((a->W + TX - 1) / TX, (a->H + TY - 1) / TY), block(TX, TY);
-  post_forward_kernel<false><<<grid, block, 0, (cudaStream_t)a->stream>>>(
+  post_forward_kernel<false><<<grid, block, 0, LS((cudaStream_t)a->stream)>>>(
       a->W, a->H, a->depth_ratio, a->allmap, a->viewmatrix, a->projmatrix, a->rend_normal,
       a->surf_depth, a->surf_normal, LossTerms(), nullptr, nullptr);
   cudaError_t e = cudaGetLastError();
@@ -397,7 +397,7 @@ int dssr_post_backward(const dssr_post_backward_args *a) {
   if (!a->allmap || !a->viewmatrix || !a->projmatrix || !a->dL_dallmap)
     return splat_fail("dssr_post_backward: NULL pointer");
   dim3 grid((a->W + TX - 1) / TX, (a->H + TY - 1) / TY), block(TX, TY);
-  post_backward_kernel<false><<<grid, block, 0, (cudaStream_t)a->stream>>>(
+  post_backward_kernel<false><<<grid, block, 0, LS((cudaStream_t)a->stream)>>>(
       a->W, a->H, a->depth_ratio, a->allmap, a->viewmatrix, a->projmatrix, a->dL_drend_normal,
       a->dL_dsurf_depth, a->dL_dsurf_normal, a->dL_dallmap, LossTerms(), nullptr, nullptr);
   cudaError_t e = cudaGetLastError();
@@ -414,7 +414,7 @@ int dssr_post_loss_forward(const dssr_post_loss_forward_args *a) {
   static_assert(sizeof(LossWorkspace) <= DSSR_POST_LOSS_WORKSPACE_BYTES, "workspace size");
   LossTerms lt{a->gt_depth, a->gt_valid, a->lambda_normal, a->lambda_alpha};
   dim3 grid((a->W + TX - 1) / TX, (a->H + TY - 1) / TY), block(TX, TY);
-  post_forward_kernel<true><<<grid, block, 0, (cudaStream_t)a->stream>>>(
+  post_forward_kernel<true><<<grid, block, 0, LS((cudaStream_t)a->stream)>>>(
       a->W, a->H, a->depth_ratio, a->allmap, a->viewmatrix, a->projmatrix, a->rend_normal,
       a->surf_depth, a->surf_normal, lt, (LossWorkspace *)a->workspace, a->losses);
   cudaError_t e = cudaGetLastError();
@@ -429,7 +429,7 @@ int dssr_post_loss_backward(const dssr_post_loss_backward_args *a) {
     return splat_fail("dssr_post_loss_backward: NULL pointer");
   LossTerms lt{a->gt_depth, a->gt_valid, a->lambda_normal, a->lambda_alpha};
   dim3 grid((a->W + TX - 1) / TX, (a->H + TY - 1) / TY), block(TX, TY);
-  post_backward_kernel<true><<<grid, block, 0, (cudaStream_t)a->stream>>>(
+  post_backward_kernel<true><<<grid, block, 0, LS((cudaStream_t)a->stream)>>>(
       a->W, a->H, a->depth_ratio, a->allmap, a->viewmatrix, a->projmatrix, nullptr, nullptr,
       nullptr, a->dL_dallmap, lt, a->losses, a->dL_dlosses);
   cudaError_t e = cudaGetLastError();

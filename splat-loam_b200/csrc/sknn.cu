@@ -12,7 +12,7 @@
 // and keeps the three smallest returns the same floats.  Here: a Morton order too (our own
 // radix sort), but at up to 20 bits per axis instead of 10 (the reference's 10-bit cells
 // are ~25 cm on an accumulated LiDAR cloud, hundreds of points each), and an implicit
-// 8-ary box hierarchy over 32-point leaves that each point descends with a small stack, so
+// 8-ary box hierarchy over KNN_LEAF-point (16) leaves that each point descends with a small stack, so
 // the work per point is O(log P) box tests and a handful of leaves, and no cudaMalloc /
 // host round trip happens inside the call.
 #include <cfloat>
@@ -202,7 +202,7 @@ morton_kernel(int P, const float *__restrict__ pts, const float *__restrict__ bb
   }
 }
 
-// sorted order -> float4(x, y, z, bits(original index)) and the 32-point leaf boxes
+// sorted order -> float4(x, y, z, bits(original index)) and the LEAF-point leaf boxes
 __global__ void __launch_bounds__(256)
 gather_leaf_kernel(int P, const float *__restrict__ pts,
                    const unsigned long long *__restrict__ words, int idx_bits, float4 *sorted,
@@ -259,9 +259,10 @@ __device__ __forceinline__ void update3(const float4 &q, const float4 &p, float 
   if (b2 > dist) { b2 = dist; }
 }
 
-// One WARP = the 32 Morton-consecutive points of one leaf, walking the hierarchy TOGETHER: a
-// node is entered when ANY lane's box distance is within that lane's current third-best, and a
-// leaf's 32 points are then offered to all 32 queries (uniform loads, every lane busy).  A
+// One WARP = 32 Morton-consecutive points (32 / LEAF neighbouring leaves), walking the hierarchy
+// TOGETHER: a node is entered when ANY lane's box distance is within that lane's current
+// third-best, and a leaf's LEAF points are then offered to all 32 queries (uniform loads, every
+// lane busy).  A
 // per-thread walk of the same tree ran at 9 of 32 lanes (the lanes' prunings differ slightly, so
 // they drift apart): 11.8 ms at 4 M points.  Offering a query more candidates than it needs
 // cannot change its three smallest distances, so the result is the same set of floats.
@@ -346,8 +347,8 @@ int sknn_dist2(int P, const float *points, float *mean_dists, void *workspace,
     return splat_fail("sknn_dist2: memset failed: %s", cudaGetErrorString(cudaGetLastError()));
   int bb = (P + 255) / 256;
   if (bb > BB_BLOCKS) bb = BB_BLOCKS;
-  bbox_partial_kernel<<<bb, 256, 0, st>>>(P, points, partial);
-  bbox_final_kernel<<<1, 32, 0, st>>>(bb, partial, num, P);
+  bbox_partial_kernel<<<bb, 256, 0, LS(st)>>>(P, points, partial);
+  bbox_final_kernel<<<1, 32, 0, LS(st)>>>(bb, partial, num, P);
   const KnnPlan plan(P);
   MortonParams mp;
   mp.idx_bits = plan.idx_bits;
@@ -358,14 +359,14 @@ int sknn_dist2(int P, const float *points, float *mean_dists, void *workspace,
     mp.bits[i] = plan.bits[i];
   }
   int mg = (P + 255) / 256;
-  if (mg > 148 * 4) mg = 148 * 4;
-  morton_kernel<<<mg, 256, 0, st>>>(P, points, partial + BB_BLOCKS * 6, wa, hist, mp);
+  if (mg > splat_sm_count() * 4) mg = splat_sm_count() * 4;
+  morton_kernel<<<mg, 256, 0, LS(st)>>>(P, points, partial + BB_BLOCKS * 6, wa, hist, mp);
   launch_digit_scan(hist, digit_base, plan.npass, nullptr, nullptr, 0, -1, HIST_REPL, st);
   unsigned long long *res = launch_sort_passes(wa, wb, nullptr, nullptr, num, (uint32_t)P, status,
                                                L.status_off, tickets, digit_base, plan.npass,
                                                plan.shift, plan.bits, 0, plan.idx_bits, (uint32_t)P, st);
   const int leaves = (P + LEAF - 1) / LEAF;
-  gather_leaf_kernel<<<(leaves * LEAF + 255) / 256, 256, 0, st>>>(P, points, res, plan.idx_bits,
+  gather_leaf_kernel<<<(leaves * LEAF + 255) / 256, 256, 0, LS(st)>>>(P, points, res, plan.idx_bits,
                                                                   sorted, boxes);
   KnnLevels lv;
   lv.nlevel = L.nlevel;
@@ -374,10 +375,10 @@ int sknn_dist2(int P, const float *points, float *mean_dists, void *workspace,
     lv.off[l] = (uint32_t)L.box_off[l];
   }
   for (int l = 1; l < L.nlevel; l++)
-    level_kernel<<<(L.cnt[l] + 255) / 256, 256, 0, st>>>(L.cnt[l], L.cnt[l - 1],
+    level_kernel<<<(L.cnt[l] + 255) / 256, 256, 0, LS(st)>>>(L.cnt[l], L.cnt[l - 1],
                                                          boxes + 2 * L.box_off[l - 1],
                                                          boxes + 2 * L.box_off[l]);
-  query_kernel<<<(P + 127) / 128, 128, 0, st>>>(P, sorted, boxes, lv, mean_dists);
+  query_kernel<<<(P + 127) / 128, 128, 0, LS(st)>>>(P, sorted, boxes, lv, mean_dists);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return splat_fail("sknn_dist2: launch failed: %s", cudaGetErrorString(e));
   return 0;

@@ -12,7 +12,7 @@ import splat_b200_native as _n
 
 _lib = _n.load()
 
-# Capacity hints for the binning buffer, keyed by (device, P, H, W): with a hint the
+# Capacity hints for the binning buffer, keyed by (device, H, W): with a hint the
 # whole frame is enqueued before the host reads the instance count, so the per-forward
 # host<->device round trip of the reference (rasterizer_impl.cu:216-219) does not stall
 # the GPU.  SPLAT_B200_HINT=0 restores the exact-size two-phase behaviour.
@@ -80,7 +80,7 @@ def rasterize_gaussians(means3D, opacity, scales, rotations, scale_modifier, tra
         means3D_c, opacity_c = _f32(means3D), _f32(opacity)
         scales_c, rot_c, pre_c = _f32(scales), _f32(rotations), _f32(transMat_precomp)
         view_c, proj_c = _f32(viewmatrix), _f32(projmatrix)
-        key = (dev.index, P, H, W)
+        key = (dev.index, H, W)     # (P changes with every densification: not part of the key)
         hint = _hints.get(key, 0) if _USE_HINT else 0
         a = _n.DssrForwardArgs(
             P, W, H, float(scale_modifier), int(bool(prefiltered)), int(bool(debug)),
@@ -122,16 +122,17 @@ def rasterize_gaussians_backward(means3D, radii, scales, rotations, scale_modifi
                                or tuple(packed.shape) != (P, 10) or packed.device != dev):
         raise RuntimeError("packed must be a contiguous float32 CUDA tensor of shape [P,10]")
     with torch.cuda.device(dev):
-        # one allocation, seven contiguous slices (the reference does seven torch::zeros,
-        # rasterize_points.cu:116-122; the kernels here write every element themselves)
-        cuts = (3, 3, 3, 1, 12, 2, 4)
-        starts, o = [], 0
-        for c in cuts:           # every slice starts 256-byte aligned (float4 accesses)
-            starts.append(o)
-            o += (c * P + 63) // 64 * 64
-        flat = torch.empty(o, dtype=torch.float32, device=dev)
-        views = [flat[b:b + c * P].view(P, c) for b, c in zip(starts, cuts)]
-        dmeans3D, dmeans2D, dnormal, dopacity, dtrans, dscales, drot = views
+        # The reference does seven torch::zeros (rasterize_points.cu:116-122); the kernels
+        # here write every element themselves, so torch.empty.  What autograd hands to a leaf
+        # as .grad gets a tensor of its own (a view of one big block would keep the whole block
+        # alive for as long as the leaf keeps its .grad); the two per-surfel intermediates
+        # (dL_dnormal, dL_dtransMat) share one.
+        f32 = dict(dtype=torch.float32, device=dev)
+        dmeans3D, dmeans2D = torch.empty((P, 3), **f32), torch.empty((P, 3), **f32)
+        dopacity, dscales = torch.empty((P, 1), **f32), torch.empty((P, 2), **f32)
+        drot = torch.empty((P, 4), **f32)
+        inner = torch.empty(15 * P, **f32)
+        dtrans, dnormal = inner[:12 * P].view(P, 12), inner[12 * P:].view(P, 3)
         if P:
             means3D_c, scales_c, rot_c = _f32(means3D), _f32(scales), _f32(rotations)
             pre_c, view_c, proj_c = _f32(transMat_precomp), _f32(viewmatrix), _f32(projmatrix)

@@ -88,11 +88,28 @@ class PeerExchange:
                 self.handle, torch.cuda.current_stream(self.device).cuda_stream))
         return self.result
 
+    def check(self):
+        """Synchronise the current stream and raise if this or ANY peer rank gave up waiting
+        during an exchange: a rank that times out marks every rank's arena before it goes on, so
+        all ranks fail here together and none applies the stale sums."""
+        torch.cuda.current_stream(self.device).synchronize()
+        code = int(self._lib.splat_xchg_fault(self.handle))
+        if code:
+            raise RuntimeError(
+                f"peer-memory exchange: a wait for rank {(code - 1) // 16} gave up in step "
+                f"{(code - 1) % 16}; the summed gradients of this window are invalid on every rank")
+
     def close(self):
         if self.handle:
             self.result = None
             self._lib.splat_xchg_destroy(self.handle)
             self.handle = ctypes.c_void_p()
+
+    def __del__(self):      # the arena (device memory + IPC mappings) must not outlive us
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def shard_keyframes(num_keyframes, rank, world_size):
@@ -163,9 +180,10 @@ class KeyframeWindow:
             return dist.get_rank(self.group), dist.get_world_size(self.group)
         return 0, 1
 
-    def accumulate(self, params, cameras, dL_dout_fn):
-        """Local part: sum of the [P,10] gradients of this rank's keyframes (no communication)."""
-        rank, world = self._world()
+    def accumulate(self, params, cameras, dL_dout_fn, local_only=False):
+        """Local part: sum of the [P,10] gradients of this rank's keyframes (no communication).
+        `local_only`: of ALL keyframes, i.e. the whole window on this GPU alone."""
+        rank, world = (0, 1) if local_only else self._world()
         P = params[0].shape[0]
         if self._buf is None or self._buf.shape[0] != P or self._buf.device != params[0].device:
             self._buf = torch.empty((P, GRAD_COLS), dtype=torch.float32, device=params[0].device)
@@ -179,8 +197,11 @@ class KeyframeWindow:
                 buf += g
         return buf, mine
 
-    def gradients(self, params, cameras, dL_dout_fn):
-        """Summed [P,10] gradient of the whole window, identical on every rank."""
+    def gradients(self, params, cameras, dL_dout_fn, check=True):
+        """Summed [P,10] gradient of the whole window, identical on every rank.  With `check`
+        (peer-memory path) the stream is synchronised and an exchange in which any rank gave
+        up waiting raises on every rank, before anybody applies the result; pass False to keep
+        the step asynchronous and call `exchange_check()` before the optimizer step instead."""
         rank, world = self._world()
         xchg = self._peer_exchange(params[0].shape[0], params[0].device) if world > 1 else None
         if xchg is None:
@@ -200,7 +221,14 @@ class KeyframeWindow:
                           accumulate=j > 0, xchg=xchg if j == len(mine) - 1 else None)
         if not mine:
             xchg.push(None)
-        return xchg.allreduce()
+        res = xchg.allreduce()
+        if check:
+            xchg.check()
+        return res
+
+    def exchange_check(self):
+        if self._xchg is not None:
+            self._xchg.check()
 
     @staticmethod
     def split(buf):

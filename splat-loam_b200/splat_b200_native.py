@@ -114,6 +114,7 @@ EXPORTS = (
     "splat_xchg_push", "splat_xchg_reduce", "splat_xchg_wait", "splat_xchg_allreduce",
     "splat_xchg_result", "splat_xchg_destroy", "dssr_post_forward", "dssr_post_backward",
     "dssr_post_loss_forward", "dssr_post_loss_backward", "splat_activation_adam_step",
+    "splat_xchg_fault", "splat_launch_count",
 )
 XCHG_HANDLE_BYTES = 64
 
@@ -188,6 +189,10 @@ def load():
     lib.splat_xchg_result.argtypes = [vp]
     lib.splat_xchg_result.restype = vp
     lib.splat_xchg_destroy.argtypes = [vp]
+    lib.splat_xchg_fault.argtypes = [vp]
+    lib.splat_xchg_fault.restype = ctypes.c_int
+    lib.splat_launch_count.argtypes = []
+    lib.splat_launch_count.restype = ctypes.c_ulonglong
     for f in (lib.splat_xchg_create, lib.splat_xchg_export, lib.splat_xchg_connect,
               lib.splat_xchg_connect_local, lib.splat_xchg_push, lib.splat_xchg_reduce,
               lib.splat_xchg_wait, lib.splat_xchg_allreduce, lib.splat_xchg_destroy):
@@ -208,6 +213,11 @@ def profile_read():
     ms = (ctypes.c_float * 16)()
     n = load().splat_profile_read(16, names, ms)
     return {names[i].decode(): float(ms[i]) for i in range(n)}
+
+
+def launch_count():
+    """Kernels launched by the library so far in this process."""
+    return int(load().splat_launch_count())
 
 
 def last_error():

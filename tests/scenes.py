@@ -14,6 +14,7 @@ CONFIGS = {
     "C2": (64, 1024, 33.2, 500000, 1),
     "C3": (64, 2048, 26.9, 1000000, 8),
     "C4": (128, 2048, 45.0, 2000000, 32),
+    "C5": (128, 2048, 45.0, 4000000, 1),   # dense depth/normal render stress (4 M surfels)
 }
 
 

@@ -22,7 +22,7 @@ def test_header_symbols_exported(native_lib):
         assert hasattr(native_lib, s), f"{s} declared in the header but not exported"
     import splat_b200_native as n
     assert sorted(n.EXPORTS) == sorted(s for s in syms)
-    assert native_lib.splat_abi_version() == 7
+    assert native_lib.splat_abi_version() == 8
 
 
 def test_no_cuda_runtime_static_state(native_lib):

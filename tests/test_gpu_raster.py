@@ -104,10 +104,12 @@ def test_against_cpu_oracle():
         assert rel_l2(r["grad_" + k], ref) < 5e-3, k
 
 
-@pytest.mark.parametrize("cfg", ["C1", "C2"])
+@pytest.mark.parametrize("cfg", ["C1", "C2", "C3", "C4", "C5"])
 def test_against_reference_build(cfg):
-    """Bit-exactness at the benchmark sizes against the unmodified reference CUDA build
-    (oracle/_ref, compiled from /root/reference by oracle/Makefile)."""
+    """Bit-exactness at every BASELINE.json size against the unmodified reference CUDA build
+    (oracle/_ref, compiled from /root/reference by oracle/Makefile): C1, the headline C2, the
+    window configs' frames C3 (64x2048, 1 M surfels) and C4 (128x2048, 2 M), and the C5 dense
+    render (4 M surfels at 128x2048)."""
     import reflib
     if not reflib.available():
         pytest.skip("oracle/_ref/libref_splat.so not built")
@@ -180,7 +182,7 @@ def test_capacity_hint_paths_agree(monkeypatch):
         monkeypatch.setattr(_C, "_USE_HINT", hint != 0)
         _C._hints.clear()
         if hint:
-            _C._hints[(c["means3D"].device.index, s["means3D"].shape[0], s["H"], s["W"])] = hint
+            _C._hints[(c["means3D"].device.index, s["H"], s["W"])] = hint
         R, out, radii, geom, binning, img = _C.rasterize_gaussians(
             c["means3D"], c["opacities"], c["scales"], c["rotations"], 1.0, empty,
             c["viewmatrix"], c["projmatrix"], s["H"], s["W"], False, False)
@@ -218,6 +220,32 @@ def test_autograd_surface_and_renderer_usage():
     vis = GaussianRasterizer(rs).markVisible(c["means3D"])
     d = c["means3D"].norm(dim=1)
     assert torch.equal(vis, (d > 0.1) & (d <= 120.0))
+
+
+@pytest.mark.parametrize("cfg,keyframe", [("C1", 3), ("C2", 7)])
+def test_mark_visible_matches_reference(cfg, keyframe):
+    """checkFrustum / markVisible (rasterizer_impl.cu:48-58,117-122) against the reference
+    build at a pose that is neither the identity nor a pure rotation: the range test is taken
+    on |view * p|, whose float rounding depends on the translation."""
+    import reflib
+    if not reflib.available():
+        pytest.skip("oracle/_ref/libref_splat.so not built")
+    from diff_surfel_spherical_rasterization import _C
+    s = scenes.make_scene(cfg, keyframe=keyframe)
+    c = to_cuda(s)
+    # put a band of points right at the two range limits, where one ulp decides
+    P = c["means3D"].shape[0]
+    g = torch.Generator(device="cuda").manual_seed(5)
+    d = torch.nn.functional.normalize(torch.randn(P // 4, 3, device="cuda", generator=g))
+    r = torch.where(torch.arange(P // 4, device="cuda") % 2 == 0, 0.1, 120.0)
+    r = r * (1.0 + 1e-6 * torch.randn(P // 4, device="cuda", generator=g))
+    t = torch.from_numpy(scenes.pose(keyframe)[:3, 3].astype(np.float32)).cuda()
+    c["means3D"] = torch.cat([c["means3D"], d * r[:, None] + t]).contiguous()
+    got = _C.mark_visible(c["means3D"], c["viewmatrix"], c["projmatrix"])
+    want = reflib.mark_visible(c["means3D"], c["viewmatrix"], c["projmatrix"])
+    assert got.dtype == torch.bool and got.shape == want.shape
+    assert 0 < int(want.sum()) < want.numel()
+    assert torch.equal(got, want)
 
 
 def test_empty_and_degenerate_inputs():
