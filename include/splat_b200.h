@@ -314,6 +314,30 @@ SPLAT_API int splat_profile_enable(int on);
 SPLAT_API int splat_profile_select(const char *stage);
 SPLAT_API int splat_profile_read(int max_stages, const char **names, float *ms);
 
+/* ---- pruning / growing the parameter tensors and their optimizer moments -----------
+ * Replaces the tensor surgery of scene/gaussian_model.py:223-316 (_prune_optimizer,
+ * prune_points, cat_tensors_to_optimizer, densification_postfix), which indexes / concatenates
+ * every parameter and every Adam moment separately.  Up to SPLAT_SURGERY_MAX_TENSORS row-major
+ * float tensors that share their row index (row width width[t] floats) go through one kernel.
+ *   splat_compact_plan   scans keep[P] (non-zero = keep) into `workspace`
+ *                        (splat_compact_workspace_bytes(P) bytes, device) and returns the
+ *                        number of kept rows in *count (synchronises `stream`: the caller
+ *                        sizes the new tensors with it - the one host round trip);
+ *   splat_compact_rows   dst[t][r] = src[t][i] for the r-th kept row i (same keep, workspace);
+ *   splat_append_rows    dst[t] = [src[t] (n_old rows); ext[t] (n_new rows)], ext == NULL or
+ *                        ext[t] == NULL appends zeros (fresh moments).
+ * dst must not alias src. */
+#define SPLAT_SURGERY_MAX_TENSORS 12
+SPLAT_API size_t splat_compact_workspace_bytes(int P);
+SPLAT_API int splat_compact_plan(int P, const unsigned char *keep, void *workspace, int *count,
+                                 void *stream);
+SPLAT_API int splat_compact_rows(int P, const unsigned char *keep, const void *workspace,
+                                 int ntensors, const float *const *src, float *const *dst,
+                                 const int *width, void *stream);
+SPLAT_API int splat_append_rows(int n_old, int n_new, int ntensors, const float *const *src,
+                                const float *const *ext, float *const *dst, const int *width,
+                                void *stream);
+
 /* Number of kernels this library has launched so far in this process (all threads, all
  * devices).  No counterpart in the reference.  A harness takes the difference around a timed
  * region to report how many of the library's kernels ran in it. */

@@ -22,6 +22,7 @@ SOURCES = [
     "peer_exchange.cu",
     "render_post.cu",
     "adam_step.cu",
+    "state_surgery.cu",
 ]
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-lineinfo",

@@ -124,16 +124,22 @@ struct BinHeader {
   // byte offset (from the aligned buffer start) of sub_mask: the backward only knows
   // num_rendered, not the capacity the forward laid the buffer out with
   unsigned long long off_sub_mask;
-  uint32_t pad2[2];
+  // what the forward compositing leaves for the backward (see dssr_render_fwd.cu): per 4x4
+  // sub-tile plane s (16 planes), blend_bits[s][bits_stride] holds one word per 32-entry step
+  // of the sub-tile's walk (bit i: entry i of the step was blended by some pixel) and
+  // pix_mask[s][capacity] the 16-bit mask of the pixels that blended each such entry
+  unsigned long long off_blend_bits, off_pix_mask;
+  uint32_t bits_stride, pix_stride;
 };
 
 struct BinLayout {
-  size_t words_a, words_b, keys, point_list, sub_mask, keys_unsorted, hist, digit_base, status,
-      tickets, total;
+  size_t words_a, words_b, keys, point_list, sub_mask, blend_bits, pix_mask, keys_unsorted, hist,
+      digit_base, status, tickets, total;
+  uint32_t bits_stride, pix_stride;
   size_t status_bytes, hist_bytes;
   size_t status_off[SORT_MAX_PASSES];  // element offset of each pass in `status`
   int nblk;
-  __host__ BinLayout(size_t C, int keep_unsorted, const SortPlan &sp) {
+  __host__ BinLayout(size_t C, int keep_unsorted, const SortPlan &sp, int ntiles) {
     nblk = (int)((C + SORT_MIN_BLOCK_ELEMS - 1) / SORT_MIN_BLOCK_ELEMS);
     if (nblk < 1) nblk = 1;
     size_t o = align_up(sizeof(BinHeader), 256);
@@ -144,6 +150,11 @@ struct BinLayout {
     words_a = o;    o = align_up(o + C * 8, 256);
     words_b = o;    o = align_up(o + C * 8, 256);
     sub_mask = o;   o = align_up(o + C * 2, 256);
+    // a step word of tile t, step k lives at (range.x >> 5) + t + k: unique per (tile, step)
+    bits_stride = (uint32_t)((C >> 5) + (size_t)ntiles + 2);
+    pix_stride = (uint32_t)align_up(C, 128);
+    blend_bits = o; o = align_up(o + (size_t)16 * bits_stride * 4, 256);
+    pix_mask = o;   o = align_up(o + (size_t)16 * pix_stride * 2, 256);
     keys_unsorted = o;
     if (keep_unsorted) o = align_up(o + C * 8, 256);
     // [hist | tickets | status] are zeroed with ONE memset per forward
@@ -195,7 +206,10 @@ struct BinView {
   unsigned long long *words_a, *words_b, *keys, *keys_unsorted;
   uint32_t *point_list;
   uint16_t *sub_mask;     // per sorted instance: which 4x4 sub-tiles of its tile it can touch
-  size_t off_sub_mask;
+  size_t off_sub_mask, off_blend_bits, off_pix_mask;
+  uint32_t *blend_bits;   // [16][bits_stride]
+  uint16_t *pix_mask;     // [16][pix_stride]
+  uint32_t bits_stride, pix_stride;
   uint32_t *hist, *digit_base, *status, *tickets;
   size_t status_off[SORT_MAX_PASSES];
   size_t zero_bytes;  // [hist .. end of status) is one contiguous region to clear
@@ -234,8 +248,8 @@ static inline ImageView make_image_view(const char *buf, int W, int H) {
   return v;
 }
 static inline BinView make_bin_view(const char *buf, size_t C, int keep_unsorted,
-                                    const SortPlan &sp) {
-  BinLayout L(C, keep_unsorted, sp);
+                                    const SortPlan &sp, int ntiles) {
+  BinLayout L(C, keep_unsorted, sp, ntiles);
   char *b = align_ptr(buf);
   BinView v;
   v.hdr = (BinHeader *)b;
@@ -246,6 +260,12 @@ static inline BinView make_bin_view(const char *buf, size_t C, int keep_unsorted
   v.point_list = (uint32_t *)(b + L.point_list);
   v.sub_mask = (uint16_t *)(b + L.sub_mask);
   v.off_sub_mask = L.sub_mask;
+  v.off_blend_bits = L.blend_bits;
+  v.off_pix_mask = L.pix_mask;
+  v.blend_bits = (uint32_t *)(b + L.blend_bits);
+  v.pix_mask = (uint16_t *)(b + L.pix_mask);
+  v.bits_stride = L.bits_stride;
+  v.pix_stride = L.pix_stride;
   v.hist = (uint32_t *)(b + L.hist);
   v.digit_base = (uint32_t *)(b + L.digit_base);
   v.status = (uint32_t *)(b + L.status);

@@ -140,10 +140,10 @@ int run_binning_and_render(const dssr_forward_args *a, const FwdParams &fp,
                            uint32_t capacity, uint32_t n_estimate, cudaStream_t st) {
   const int keep = (a->debug & 2) ? 1 : 0;
   const bool dbg = a->debug & 1;
-  BinLayout bl(capacity, keep, sp);
+  BinLayout bl(capacity, keep, sp, iv.tiles);
   char *bptr = a->binning_alloc(a->binning_ctx, bl.total);
   if (!bptr) return fail("binning_alloc(%zu) returned NULL", bl.total);
-  BinView bv = make_bin_view(bptr, capacity, keep, sp);
+  BinView bv = make_bin_view(bptr, capacity, keep, sp, iv.tiles);
   CUDA_TRY(cudaMemsetAsync(bv.hist, 0, bv.zero_bytes, st));
   {
     ProfScope ps("emit", st);
@@ -202,7 +202,7 @@ size_t dssr_image_bytes(int W, int H) { return ImageLayout(W, H).total; }
 size_t dssr_binning_bytes(int64_t capacity, int W, int H, int P, int keep_unsorted) {
   ImageLayout il(W, H);
   SortPlan sp(P, il.tiles);
-  return BinLayout((size_t)(capacity < 0 ? 0 : capacity), keep_unsorted, sp).total;
+  return BinLayout((size_t)(capacity < 0 ? 0 : capacity), keep_unsorted, sp, il.tiles).total;
 }
 
 int splat_profile_enable(int on) {
@@ -349,7 +349,7 @@ int dssr_backward(const dssr_backward_args *a) {
   SortPlan sp(a->P, il.tiles);
   GeomView gv = make_geom_view(a->geom_buffer, a->P);
   ImageView iv = make_image_view(a->image_buffer, a->W, a->H);
-  BinView bv = make_bin_view(a->binning_buffer, (size_t)a->R, 0, sp);  // only point_list is used
+  BinView bv = make_bin_view(a->binning_buffer, (size_t)a->R, 0, sp, il.tiles);  // only point_list and the header are used
   BwdParams bp;
   bp.P = a->P; bp.W = a->W; bp.H = a->H;
   bp.scales = a->scales; bp.rotations = a->rotations;
@@ -415,7 +415,7 @@ int dssr_debug_state(const char *geom_buffer, const char *binning_buffer,
     BinHeader bh;
     CUDA_TRY(cudaMemcpy(&bh, align_ptr(binning_buffer), sizeof bh, cudaMemcpyDeviceToHost));
     if (bh.magic != 0x42494e31u) return fail("dssr_debug_state: not a binning buffer");
-    bv = make_bin_view(binning_buffer, bh.capacity, bh.keep_unsorted, sp);
+    bv = make_bin_view(binning_buffer, bh.capacity, bh.keep_unsorted, sp, iv.tiles);
   }
   const std::string n(name);
   if (n == "depths") { *ptr = gv.depths; *count = P; }

@@ -5,15 +5,26 @@
 //   preprocessCUDA<3> (backward) backward.cu:377-396 with compute_transmat_aabb :303-375
 //   quat_to_rotmat_vjp          auxiliary.h:300-339
 //
-// The reference issues 13 global float atomicAdds per (pixel, surfel) pair, all 256
-// threads of a tile hitting the same 13 addresses.  Here a warp owns a 4x4 pixel
-// sub-tile, walks its tile's list back to front from the furthest entry any of its
-// pixels blended, skips entries whose cull box misses the sub-tile (exact, see
-// dssr_render_fwd.cu), evaluates the survivors two at a time (one per half warp) and
-// reduces each surfel's 13 per-pixel contributions inside its half warp with a
-// 15-shuffle transposed butterfly, after which 13 lanes issue ONE atomic instruction
-// (one RED per component per sub-tile instead of one per pixel).  The reference's backward is not the adjoint of its forward (SURVEY.md §8 a10,
-// quirks Q1-Q4, Q7); it is reproduced as written.
+// The reference re-walks every tile list with 256 threads, repeats the forward's tests at every
+// (pixel, entry) pair and issues 13 global float atomicAdds per surviving pair, all threads of
+// a tile hitting the same 13 addresses.  Here the forward has already written down WHICH pairs
+// it blended (dssr_render_fwd.cu: one word per 32-entry step and a pixel mask per blended
+// entry), and those are exactly the pairs the reference's backward ends up processing
+// (backward.cu:132 skips entries past a pixel's last contributor, :152-182 repeat the
+// forward's tests on the same floats).  So the backward tests nothing:
+//   * a warp owns an 8x4 pixel block (two 4x4 sub-tiles) and walks its tile's list back to
+//     front; per 32-entry step it reads the two step words, and only the blended entries'
+//     records (64 B, L2-resident) and pixel masks;
+//   * the blended (pixel, entry) pairs are laid end to end and processed 32 at a time, ONE PAIR
+//     PER LANE whatever its pixel and entry (P1: intersection, alpha, depth);
+//   * the per-pixel recurrences (backward.cu:183-237: T, the accum_* terms, last_dL_dT), the
+//     only sequential part, run on the pixel's own lane over that pixel's pairs of the batch,
+//     in list order, from shared memory (P2);
+//   * back on the pair lanes the gradient of the pair w.r.t. the surfel's 13 values is
+//     finished (P3), the batch's contributions are summed per entry through shared memory and
+//     one atomic per (entry, component) goes out.
+// The reference's backward is not the adjoint of its forward (SURVEY.md §8 a10, quirks Q1-Q4,
+// Q7); it is reproduced as written.
 #include "peer_exchange.cuh"
 #include "raster_math.cuh"
 
@@ -31,8 +42,11 @@ __device__ __forceinline__ unsigned long long btime() {
 
 namespace {
 
-constexpr int SUB = 4;                                            // 4x4 pixels per warp
+constexpr int SUB = 4;                                            // 4x4 pixels per sub-tile
 constexpr int SUBS_PER_TILE = (SPLAT_TILE / SUB) * (SPLAT_TILE / SUB);   // 16
+constexpr int UNITS_PER_TILE = SUBS_PER_TILE / 2;                 // a warp = two sub-tiles
+constexpr int ENT_CAP = 64;        // blended entries staged per warp
+constexpr int GATHER_PAIRS = 64;   // entries are gathered until they hold this many pairs
 
 // Per-pixel state of the reverse traversal (backward.cu:62-98) and its constants.
 struct BackState {
@@ -41,13 +55,13 @@ struct BackState {
 };
 struct PixelConst {
   float gD, gA, gN0, gN1, gN2, gMed, gReg, final_D, final_D2, final_A;
-  uint32_t last_contributor, median_contributor;
+  uint32_t median_contributor;
 };
 struct StepOut {
   float T, w, dL_dalpha, dLd_depth;
 };
 
-// backward.cu:183-237 for one surviving (pixel, surfel) pair, as written (quirks kept)
+// backward.cu:183-237 for one blended (pixel, surfel) pair, as written (quirks kept)
 __device__ __forceinline__ StepOut recur(BackState &b, const PixelConst &c, float alpha,
                                          float depth, float nx, float ny, float nz, uint32_t pos) {
   StepOut o;
@@ -79,62 +93,96 @@ __device__ __forceinline__ StepOut recur(BackState &b, const PixelConst &c, floa
   return o;
 }
 
-// One WARP per CTA = one 4x4 sub-tile, CTAs in order of decreasing tile list length.  Same
-// traversal machinery as the forward (sub-tile masks, double-buffered staging), walked back
-// to front; lanes 0-15 handle the later surfel of a pair, lanes 16-31 the earlier one.
+// position of the k-th (0-based) set bit of m (k < popc(m))
+__device__ __forceinline__ uint32_t select_bit(uint32_t m, uint32_t k) {
+  uint32_t pos = 0, c;
+  c = __popc(m & 0xffffu); if (k >= c) { pos = 16; k -= c; m >>= 16; }
+  c = __popc(m & 0xffu);   if (k >= c) { pos += 8; k -= c; m >>= 8; }
+  c = __popc(m & 0xfu);    if (k >= c) { pos += 4; k -= c; m >>= 4; }
+  c = __popc(m & 0x3u);    if (k >= c) { pos += 2; k -= c; m >>= 2; }
+  c = m & 1u;              if (k >= c) { pos += 1; }
+  return pos;
+}
+
+// everything a warp stages in shared memory (one warp per CTA)
+struct __align__(16) WarpStage {
+  float4 rec[ENT_CAP][4];           // the gathered entries' 64-byte records
+  float4 pout[32];                  // P2 -> P3: T, dL_dalpha, dLd_depth, w of the batch's pairs
+  uint32_t ent_id[ENT_CAP];         // surfel index
+  uint32_t ent_pos[ENT_CAP];        // position in the tile's list (the reference's `contributor`)
+  uint32_t ent_mask[ENT_CAP];       // pixels that blended it (bit = lane of the pixel)
+  uint32_t ent_prefix[ENT_CAP + 1]; // exclusive prefix of the pair counts
+  float ray[10][32];                // per pixel: X Y Z ax ay ex ey ez pxf pyf
+  float gN[3][32];                  // per pixel: dL_dout of the normal channels
+  float pa[32], pd[32];             // P1 -> P2: alpha, depth of the batch's pairs
+  uint32_t pe[32];                  // P1 -> P2: entry slot of the pair
+  uint32_t pmask[32];               // per pixel: which lanes of the batch hold its pairs
+  float vbuf[32][13];               // P3: the pairs' 13 contributions, summed per entry
+};
+
+// One WARP per CTA = one 8x4 pixel block; CTAs in order of decreasing number of pairs.
 __global__ void __launch_bounds__(32)
 render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restrict__ bwd_order,
-                       const uint32_t *__restrict__ point_list,
-                       const uint16_t *__restrict__ sub_mask_base, const BinHeader *__restrict__ bhdr,
-                       const float4 *__restrict__ rec, const float *__restrict__ projmatrix, int W,
-                       int H, int tiles_x, uint32_t P, const float *__restrict__ final_T,
-                       const uint32_t *__restrict__ n_contrib, const float *__restrict__ dL_dout,
-                       float *__restrict__ dL_dtransMat, float *__restrict__ dL_dnormal,
-                       float *__restrict__ dL_dopacity) {
-  __shared__ float4 s_rec[2][32][4];
-  __shared__ float s_cut[2][32];
-  __shared__ uint32_t s_pos[2][32];
-  __shared__ uint32_t s_id[2][32];
+                       const uint32_t *__restrict__ point_list, const char *__restrict__ bin_base,
+                       const BinHeader *__restrict__ bhdr, const float4 *__restrict__ rec,
+                       const float *__restrict__ projmatrix, int W, int H, int tiles_x, uint32_t P,
+                       const float *__restrict__ final_T, const uint32_t *__restrict__ n_contrib,
+                       const float *__restrict__ dL_dout, float *__restrict__ dL_dtransMat,
+                       float *__restrict__ dL_dnormal, float *__restrict__ dL_dopacity) {
+  __shared__ WarpStage st;
   const int lane = threadIdx.x, half = lane >> 4, p16 = lane & 15;
-  const uint32_t work = blockIdx.x;
+  const uint32_t full = 0xffffffffu;
 #ifdef RENDER_TRACE
-  if (lane == 0 && work < 8192) {   // written at once: nothing extra stays live in registers
-    g_btrace[work][0] = btime();
-    g_btrace[work][1] = 0;
+  if (lane == 0 && blockIdx.x < 8192) {
+    g_btrace[blockIdx.x][0] = btime();
+    g_btrace[blockIdx.x][1] = 0;
   }
 #endif
-  const uint32_t unit = bwd_order[work];          // sub-tiles by decreasing walk length
-  const uint32_t tile = unit / SUBS_PER_TILE;
-  const int sub = unit % SUBS_PER_TILE;
-  const int x0 = (tile % tiles_x) * SPLAT_TILE + (sub & 3) * SUB;
-  const int y0 = (tile / tiles_x) * SPLAT_TILE + (sub >> 2) * SUB;
+  const uint32_t unit = bwd_order[blockIdx.x];
+  const uint32_t tile = unit / UNITS_PER_TILE;
+  const int sub_a = 2 * (int)(unit % UNITS_PER_TILE);           // left sub-tile; right = sub_a + 1
+  const int x0 = (tile % tiles_x) * SPLAT_TILE + (sub_a & 3) * SUB;
+  const int y0 = (tile / tiles_x) * SPLAT_TILE + (sub_a >> 2) * SUB;
   if (x0 >= W || y0 >= H) return;
-  const int px = x0 + (p16 & 3), py = y0 + (p16 >> 2);
+  const int px = x0 + SUB * half + (p16 & 3), py = y0 + (p16 >> 2);
   const bool inside = px < W && py < H;
   const size_t HW = (size_t)W * H;
   const size_t pix = (size_t)py * W + px;
 
-  PixelConst pc;
-  pc.last_contributor = inside ? n_contrib[pix] : 0u;
-  uint32_t max_last = pc.last_contributor;
+  // how far each sub-tile's forward walk got: the furthest entry one of its pixels blended
+  const uint32_t last_contributor = inside ? n_contrib[pix] : 0u;
+  uint32_t max_mine = last_contributor;
 #pragma unroll
-  for (int o = 8; o > 0; o >>= 1)
-    max_last = max(max_last, __shfl_xor_sync(0xffffffffu, max_last, o));
+  for (int o = 8; o > 0; o >>= 1) max_mine = max(max_mine, __shfl_xor_sync(full, max_mine, o));
+  const uint32_t max_other = __shfl_xor_sync(full, max_mine, 16);
+  const uint32_t max_a = half ? max_other : max_mine, max_b = half ? max_mine : max_other;
+  const uint32_t max_last = max(max_a, max_b);
 #ifdef RENDER_TRACE
-  if (lane == 0 && work < 8192) g_btrace[work][2] = max_last;
+  if (lane == 0 && blockIdx.x < 8192) g_btrace[blockIdx.x][2] = max_last;
 #endif
   if (max_last == 0) return;
-  // the forward stored the offset of the mask array in the buffer's header (the capacity it
-  // was laid out with is not known to the backward's caller)
-  const uint16_t *sub_mask = reinterpret_cast<const uint16_t *>(
-      reinterpret_cast<const char *>(sub_mask_base) + bhdr->off_sub_mask);
+
+  const uint2 range = ranges[tile];
+  const uint32_t bits_stride = bhdr->bits_stride, pix_stride = bhdr->pix_stride;
+  const uint32_t *words_a = reinterpret_cast<const uint32_t *>(bin_base + bhdr->off_blend_bits) +
+                            (size_t)sub_a * bits_stride + (range.x >> 5) + tile;
+  const uint32_t *words_b = words_a + bits_stride;
+  const uint16_t *pm_a = reinterpret_cast<const uint16_t *>(bin_base + bhdr->off_pix_mask) +
+                         (size_t)sub_a * pix_stride + range.x;
+  const uint16_t *pm_b = pm_a + pix_stride;
+  const uint32_t *plist = point_list + range.x;
 
   const float fx = projmatrix[0], fy = projmatrix[5], cx = projmatrix[8], cy = projmatrix[9];
-  const PixelRay ray = make_ray((float)px, (float)py, fx, fy, cx, cy);
-  const uint2 range = ranges[tile];
-  const uint32_t lt = (1u << lane) - 1u;
+  {
+    const PixelRay r = make_ray((float)px, (float)py, fx, fy, cx, cy);
+    st.ray[0][lane] = r.X;  st.ray[1][lane] = r.Y;  st.ray[2][lane] = r.Z;
+    st.ray[3][lane] = r.ax; st.ray[4][lane] = r.ay;
+    st.ray[5][lane] = r.ex; st.ray[6][lane] = r.ey; st.ray[7][lane] = r.ez;
+    st.ray[8][lane] = r.pxf; st.ray[9][lane] = r.pyf;
+  }
 
   BackState bs;
+  PixelConst pc;
   const float T_final = inside ? final_T[pix] : 0.0f;
   bs.T = T_final;
   bs.last_dL_dT = bs.accum_depth_rec = bs.accum_alpha_rec = 0.f;
@@ -154,184 +202,201 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
     pc.gMed = dL_dout[pix + 5 * HW];
     pc.gReg = dL_dout[pix + 6 * HW];
   }
+  st.gN[0][lane] = pc.gN0; st.gN[1][lane] = pc.gN1; st.gN[2][lane] = pc.gN2;
 
-  // ---- prologue: stage the top step, fetch masks / indices of the one below ----
+  const int top_a = max_a ? (int)((max_a - 1) >> 5) : -1, top_b = max_b ? (int)((max_b - 1) >> 5) : -1;
   int chunk = (int)((max_last - 1) >> 5);
-  uint32_t m;
-  {
-    const uint32_t q = ((uint32_t)chunk << 5) + lane;
-    const bool hit = (q < max_last) && ((sub_mask[range.x + q] >> sub) & 1u);
-    m = __ballot_sync(0xffffffffu, hit);
-    if (hit) {
-      const int slot = __popc(m & lt);
-      const uint32_t id = min(point_list[range.x + q], P - 1u);
-      const float4 *r = rec + 4 * (size_t)id;
-      const float4 a = __ldg(r), b = __ldg(r + 1), c = __ldg(r + 2), d = __ldg(r + 3);
-      s_rec[0][slot][0] = a; s_rec[0][slot][1] = b; s_rec[0][slot][2] = c; s_rec[0][slot][3] = d;
-      s_cut[0][slot] = rho_cutoff(d.x);
-      s_pos[0][slot] = q;
-      s_id[0][slot] = id;
-    }
-  }
-  uint32_t nmask = 0u, nid = 0u;
-  if (chunk >= 1) {
-    const uint32_t q = ((uint32_t)(chunk - 1) << 5) + lane;
-    nmask = sub_mask[range.x + q];
-    nid = point_list[range.x + q];
-  }
+  // the step words run one step ahead of their use
+  uint32_t nword_a = chunk <= top_a ? words_a[chunk] : 0u, nword_b = chunk <= top_b ? words_b[chunk] : 0u;
+  int nent = 0;
+  uint32_t pending = 0;
   __syncwarp();
-  const uint32_t hmask = half ? 0xffff0000u : 0x0000ffffu;
-  int cur = 0;
-  for (; chunk >= 0; chunk--, cur ^= 1) {
-    // ---- issue the loads of the step below ----
-    const bool nhit = (chunk >= 1) && ((nmask >> sub) & 1u);
-    const uint32_t nm = __ballot_sync(0xffffffffu, nhit);
-    const uint32_t id1 = min(nid, P - 1u);
-    if (chunk >= 2) {
-      const uint32_t q = ((uint32_t)(chunk - 2) << 5) + lane;
-      nmask = sub_mask[range.x + q];
-      nid = point_list[range.x + q];
-    }
-    float4 na, nb, nc, nd;
-    if (nhit) {
-      const float4 *r = rec + 4 * (size_t)id1;
-      na = __ldg(r); nb = __ldg(r + 1); nc = __ldg(r + 2); nd = __ldg(r + 3);
-    }
-    // ---- this step's survivors, back to front, two at a time ----
-    const int nsurv = __popc(m);
-    for (int top = nsurv - 1; top >= 0; top -= 2) {
-      // lanes 0-15 take survivor `top` (later in the list), lanes 16-31 survivor `top - 1`
-      const int slot = top - half;
-      const bool mine = slot >= 0;
-      const int sl = mine ? slot : top;
-      const SurfelRec s = unpack_rec(s_rec[cur][sl][0], s_rec[cur][sl][1], s_rec[cur][sl][2],
-                                     s_rec[cur][sl][3]);
-      const uint32_t pos = s_pos[cur][sl];   // == the reference's `contributor` after decrement
-      Hit h;
-      const bool maybe = mine && pos < pc.last_contributor && intersect_begin(ray, s, s_cut[cur][sl], h);
-      if (!__any_sync(0xffffffffu, maybe)) continue;
-      const bool ok = maybe && intersect_finish(ray, s, h);
-      const bool ok_o = __shfl_xor_sync(0xffffffffu, (int)ok, 16) != 0;
-      const float alpha_o = __shfl_xor_sync(0xffffffffu, h.alpha, 16);
-      const float depth_o = __shfl_xor_sync(0xffffffffu, h.depth, 16);
-      const bool ok1 = half ? ok_o : ok, ok2 = half ? ok : ok_o;
-      StepOut o1, o2;
-      o1.T = o1.w = o1.dL_dalpha = o1.dLd_depth = 0.f;
-      o2 = o1;
-      if (ok1) {
-        const float4 c = s_rec[cur][top][2];
-        o1 = recur(bs, pc, half ? alpha_o : h.alpha, half ? depth_o : h.depth, c.y, c.z, c.w,
-                   s_pos[cur][top]);
+
+  while (true) {
+    // ---- gather blended entries, back to front, until they hold enough pairs ----
+    while (chunk >= 0 && pending < GATHER_PAIRS && nent + 32 <= ENT_CAP) {
+      const uint32_t word_a = nword_a, word_b = nword_b;
+      if (chunk >= 1) {
+        nword_a = chunk - 1 <= top_a ? words_a[chunk - 1] : 0u;
+        nword_b = chunk - 1 <= top_b ? words_b[chunk - 1] : 0u;
       }
-      if (ok2) {
-        const float4 c = s_rec[cur][top - 1][2];
-        o2 = recur(bs, pc, half ? h.alpha : alpha_o, half ? h.depth : depth_o, c.y, c.z, c.w,
-                   s_pos[cur][top - 1]);
-      }
-      // each half finishes the gradient of ITS surfel
-      if ((__ballot_sync(0xffffffffu, ok) & hmask) == 0u) continue;
-      const StepOut o = half ? o2 : o1;
-      float v[16];
-#pragma unroll
-      for (int i = 0; i < 16; i++) v[i] = 0.0f;
-      if (ok) {
-        const float alpha = h.alpha, depth = h.depth, T = o.T, dL_dalpha = o.dL_dalpha,
-                    dLd_depth = o.dLd_depth;
-        v[9] = o.w * pc.gN0;
-        v[10] = o.w * pc.gN1;
-        v[11] = o.w * pc.gN2;
-        v[12] = h.G * dL_dalpha;   // Q1: the 0.99 clamp is ignored here
-        if (h.rho3d <= h.rho2d) {
-          const float inv_depth = 1.0f / depth;
-          const float bTu = s.tux * h.bx + s.tuy * h.by + s.tuz * h.bz;
-          const float bTv = s.tvx * h.bx + s.tvy * h.by + s.tvz * h.bz;
-          const float adl = -alpha * dL_dalpha;
-          const float q2 = alpha * T * dLd_depth * inv_depth;   // Q2: alpha*T applied twice
-          const float dsx = adl * h.sx + bTu * q2;
-          const float dsy = adl * h.sy + bTv * q2;
-          const float ipz = 1.0f / h.pz;
-          const float dpx = dsx * ipz, dpy = dsy * ipz;
-          const float dpz = -(dsx * h.px + dsy * h.py) * (ipz * ipz);
-          // k1 = dL_dp x k, k2 = dL_dp x l
-          const float k1x = dpy * h.kz - dpz * h.ky, k1y = dpz * h.kx - dpx * h.kz,
-                      k1z = dpx * h.ky - dpy * h.kx;
-          const float k2x = dpy * h.lz - dpz * h.ly, k2y = dpz * h.lx - dpx * h.lz,
-                      k2z = dpx * h.ly - dpy * h.lx;
-          const float cu = dLd_depth * h.sx * inv_depth, cv = dLd_depth * h.sy * inv_depth,
-                      cw = dLd_depth * inv_depth;
-          v[0] = k1x * ray.ex - k2x * ray.ax + cu * h.bx;
-          v[1] = k1x * ray.ey - k2x * ray.ay + cu * h.by;
-          v[2] = k1x * ray.ez + cu * h.bz;
-          v[3] = k1y * ray.ex - k2y * ray.ax + cv * h.bx;
-          v[4] = k1y * ray.ey - k2y * ray.ay + cv * h.by;
-          v[5] = k1y * ray.ez + cv * h.bz;
-          v[6] = k1z * ray.ex - k2z * ray.ax + cw * h.bx;
-          v[7] = k1z * ray.ey - k2z * ray.ay + cw * h.by;
-          v[8] = k1z * ray.ez + cw * h.bz;
-        } else {
-          // 2D-filter branch (backward.cu:278-298), Q3 and Q7 kept
-          const float c2 = -2.0f * alpha * dL_dalpha * 2.0f;
-          const float ddx = c2 * h.dx, ddy = c2 * h.dy;
-          const float ss = s.twx * s.twx + s.twy * s.twy;
-          const float sn = sqrtf(ss);
-          const float inv_ss = 1.0f / ss, inv_snd = 1.0f / (sn * s.d2d), inv_d2d = 1.0f / s.d2d;
-          const float gx = fx * ddx, gy = fy * ddy;
-          const float cw = dLd_depth * inv_d2d;
-          v[6] = gx * (-s.twy * inv_ss) + gy * (-s.twx * s.twz * inv_snd) + cw * s.twx;
-          v[7] = gx * (s.twx * inv_ss) + gy * (-s.twy * s.twz * inv_snd) + cw * s.twy;
-          v[8] = gy * sn * inv_d2d + cw * s.twz;
+      const uint32_t vote = word_a | word_b;
+      if (vote) {
+        const bool in_a = (word_a >> lane) & 1u, in_b = (word_b >> lane) & 1u;
+        const bool any = in_a || in_b;
+        const uint32_t q = ((uint32_t)chunk << 5) + lane;
+        uint32_t mask = 0u, id = 0u;
+        if (any) {
+          id = min(plist[q], P - 1u);
+          if (in_a) mask = pm_a[q];
+          if (in_b) mask |= (uint32_t)pm_b[q] << 16;
         }
-      }
-      // transposed butterfly inside the half warp: 16 values x 16 lanes -> lane p holds v[p]
-      {
-        const bool hi = p16 & 8;
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-          float send = hi ? v[i] : v[i + 8], keep = hi ? v[i + 8] : v[i];
-          v[i] = keep + __shfl_xor_sync(hmask, send, 8);
+        float4 ra, rb, rc, rd;
+        if (any) {
+          const float4 *r = rec + 4 * (size_t)id;
+          ra = __ldg(r); rb = __ldg(r + 1); rc = __ldg(r + 2); rd = __ldg(r + 3);
         }
-      }
-      {
-        const bool hi = p16 & 4;
+        const uint32_t cnt = __popc(mask);
+        uint32_t suffix = cnt;                    // pairs of this lane's entry and of all later ones
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-          float send = hi ? v[i] : v[i + 4], keep = hi ? v[i + 4] : v[i];
-          v[i] = keep + __shfl_xor_sync(hmask, send, 4);
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t n = __shfl_down_sync(full, suffix, o);
+          if (lane + o < 32) suffix += n;
         }
-      }
-      {
-        const bool hi = p16 & 2;
-#pragma unroll
-        for (int i = 0; i < 2; i++) {
-          float send = hi ? v[i] : v[i + 2], keep = hi ? v[i + 2] : v[i];
-          v[i] = keep + __shfl_xor_sync(hmask, send, 2);
+        const uint32_t total = __shfl_sync(full, suffix, 0);
+        if (any) {
+          const int slot = nent + __popc(vote >> lane) - 1;     // later entries first
+          st.ent_id[slot] = id;
+          st.ent_pos[slot] = q;
+          st.ent_mask[slot] = mask;
+          st.ent_prefix[slot] = pending + suffix - cnt;
+          st.rec[slot][0] = ra; st.rec[slot][1] = rb; st.rec[slot][2] = rc; st.rec[slot][3] = rd;
         }
+        nent += __popc(vote);
+        pending += total;
       }
-      {
-        const bool hi = p16 & 1;
-        float send = hi ? v[0] : v[1], keep = hi ? v[1] : v[0];
-        v[0] = keep + __shfl_xor_sync(hmask, send, 1);
-      }
-      if (p16 <= 12 && v[0] != 0.0f) {
-        const size_t gid = s_id[cur][sl];
-        float *dst;
-        if (p16 < 9) dst = dL_dtransMat + gid * 12 + (p16 / 3) * 4 + (p16 % 3);
-        else if (p16 < 12) dst = dL_dnormal + gid * 3 + (p16 - 9);
-        else dst = dL_dopacity + gid;
-        atomicAdd(dst, v[0]);
-      }
+      chunk--;
     }
-    // ---- park the records of the step below in the other buffer ----
-    if (nhit) {
-      const int slot = __popc(nm & lt);
-      s_rec[cur ^ 1][slot][0] = na; s_rec[cur ^ 1][slot][1] = nb;
-      s_rec[cur ^ 1][slot][2] = nc; s_rec[cur ^ 1][slot][3] = nd;
-      s_cut[cur ^ 1][slot] = rho_cutoff(nd.x);
-      s_pos[cur ^ 1][slot] = ((uint32_t)(chunk - 1) << 5) + lane;
-      s_id[cur ^ 1][slot] = id1;
+    if (pending == 0) {
+      if (chunk < 0) break;
+      continue;
     }
-    m = nm;
+    if (lane == 0) st.ent_prefix[nent] = pending;
     __syncwarp();
+
+    // ---- composite the gathered pairs, 32 at a time ----
+    for (uint32_t base = 0; base < pending; base += 32) {
+      const uint32_t g = base + lane;
+      const bool valid = g < pending;
+      // P1: which (entry, pixel) is pair g?  binary search over the prefix sums
+      int j = 0;
+#pragma unroll
+      for (int s = ENT_CAP / 2; s > 0; s >>= 1) {
+        const int j2 = j + s;
+        if (j2 < nent && st.ent_prefix[j2] <= g) j = j2;
+      }
+      const uint32_t emask = st.ent_mask[j];
+      const int pixel = valid ? (int)select_bit(emask, g - st.ent_prefix[j]) : lane;
+      const SurfelRec s = unpack_rec(st.rec[j][0], st.rec[j][1], st.rec[j][2], st.rec[j][3]);
+      PixelRay ray;
+      ray.X = st.ray[0][pixel];  ray.Y = st.ray[1][pixel];  ray.Z = st.ray[2][pixel];
+      ray.ax = st.ray[3][pixel]; ray.ay = st.ray[4][pixel];
+      ray.ex = st.ray[5][pixel]; ray.ey = st.ray[6][pixel]; ray.ez = st.ray[7][pixel];
+      ray.pxf = st.ray[8][pixel]; ray.pyf = st.ray[9][pixel];
+      Hit h;
+      intersect_begin(ray, s, 3.0e38f, h);
+      // the forward blended this pair, so the same arithmetic passes the same tests
+      const bool ok = valid && intersect_finish(ray, s, h);
+      st.pa[lane] = h.alpha;
+      st.pd[lane] = h.depth;
+      st.pe[lane] = (uint32_t)j;
+      st.pmask[lane] = 0u;
+      __syncwarp();
+      {
+        const uint32_t peers = __match_any_sync(full, ok ? pixel : 64 + lane);
+        if (ok) st.pmask[pixel] = peers;
+      }
+      __syncwarp();
+      // P2: every pixel's lane runs its recurrences over its pairs of the batch, in list order
+      {
+        uint32_t m = st.pmask[lane];
+        while (__any_sync(full, m != 0u)) {
+          if (m) {
+            const int q = __ffs(m) - 1;
+            m &= m - 1u;
+            const uint32_t e = st.pe[q];
+            const float4 c = st.rec[e][2];
+            const StepOut o = recur(bs, pc, st.pa[q], st.pd[q], c.y, c.z, c.w, st.ent_pos[e]);
+            st.pout[q] = make_float4(o.T, o.dL_dalpha, o.dLd_depth, o.w);
+          }
+        }
+      }
+      __syncwarp();
+      // P3: the pair's contribution to its surfel's 13 values
+      {
+        float v[13];
+#pragma unroll
+        for (int i = 0; i < 13; i++) v[i] = 0.0f;
+        if (ok) {
+          const float4 o = st.pout[lane];
+          const float T = o.x, dL_dalpha = o.y, dLd_depth = o.z, w = o.w;
+          const float alpha = h.alpha, depth = h.depth;
+          v[9] = w * st.gN[0][pixel];
+          v[10] = w * st.gN[1][pixel];
+          v[11] = w * st.gN[2][pixel];
+          v[12] = h.G * dL_dalpha;   // Q1: the 0.99 clamp is ignored here
+          if (h.rho3d <= h.rho2d) {
+            const float inv_depth = 1.0f / depth;
+            const float bTu = s.tux * h.bx + s.tuy * h.by + s.tuz * h.bz;
+            const float bTv = s.tvx * h.bx + s.tvy * h.by + s.tvz * h.bz;
+            const float adl = -alpha * dL_dalpha;
+            const float q2 = alpha * T * dLd_depth * inv_depth;   // Q2: alpha*T applied twice
+            const float dsx = adl * h.sx + bTu * q2;
+            const float dsy = adl * h.sy + bTv * q2;
+            const float ipz = 1.0f / h.pz;
+            const float dpx = dsx * ipz, dpy = dsy * ipz;
+            const float dpz = -(dsx * h.px + dsy * h.py) * (ipz * ipz);
+            // k1 = dL_dp x k, k2 = dL_dp x l
+            const float k1x = dpy * h.kz - dpz * h.ky, k1y = dpz * h.kx - dpx * h.kz,
+                        k1z = dpx * h.ky - dpy * h.kx;
+            const float k2x = dpy * h.lz - dpz * h.ly, k2y = dpz * h.lx - dpx * h.lz,
+                        k2z = dpx * h.ly - dpy * h.lx;
+            const float cu = dLd_depth * h.sx * inv_depth, cv = dLd_depth * h.sy * inv_depth,
+                        cw = dLd_depth * inv_depth;
+            v[0] = k1x * ray.ex - k2x * ray.ax + cu * h.bx;
+            v[1] = k1x * ray.ey - k2x * ray.ay + cu * h.by;
+            v[2] = k1x * ray.ez + cu * h.bz;
+            v[3] = k1y * ray.ex - k2y * ray.ax + cv * h.bx;
+            v[4] = k1y * ray.ey - k2y * ray.ay + cv * h.by;
+            v[5] = k1y * ray.ez + cv * h.bz;
+            v[6] = k1z * ray.ex - k2z * ray.ax + cw * h.bx;
+            v[7] = k1z * ray.ey - k2z * ray.ay + cw * h.by;
+            v[8] = k1z * ray.ez + cw * h.bz;
+          } else {
+            // 2D-filter branch (backward.cu:278-298), Q3 and Q7 kept
+            const float c2 = -2.0f * alpha * dL_dalpha * 2.0f;
+            const float ddx = c2 * h.dx, ddy = c2 * h.dy;
+            const float ss = s.twx * s.twx + s.twy * s.twy;
+            const float sn = sqrtf(ss);
+            const float inv_ss = 1.0f / ss, inv_snd = 1.0f / (sn * s.d2d), inv_d2d = 1.0f / s.d2d;
+            const float gx = fx * ddx, gy = fy * ddy;
+            const float cw = dLd_depth * inv_d2d;
+            v[6] = gx * (-s.twy * inv_ss) + gy * (-s.twx * s.twz * inv_snd) + cw * s.twx;
+            v[7] = gx * (s.twx * inv_ss) + gy * (-s.twy * s.twz * inv_snd) + cw * s.twy;
+            v[8] = gy * sn * inv_d2d + cw * s.twz;
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 13; i++) st.vbuf[lane][i] = v[i];
+      }
+      __syncwarp();
+      // the batch's pairs of one entry are consecutive: sum them per (entry, component)
+      {
+        const int nvalid = (int)min(32u, pending - base);
+        const int j_first = __shfl_sync(full, j, 0), j_last = __shfl_sync(full, j, nvalid - 1);
+        const int tasks = (j_last - j_first + 1) * 13;
+        for (int t = lane; t < tasks; t += 32) {
+          const int seg = t / 13, comp = t - seg * 13;
+          const int e = j_first + seg;
+          const int q0 = max((int)st.ent_prefix[e] - (int)base, 0);
+          const int q1 = min((int)st.ent_prefix[e + 1] - (int)base, nvalid);
+          float sum = 0.0f;
+          for (int q = q0; q < q1; q++) sum += st.vbuf[q][comp];
+          if (sum != 0.0f) {
+            const size_t gid = st.ent_id[e];
+            float *dst;
+            if (comp < 9) dst = dL_dtransMat + gid * 12 + (comp / 3) * 4 + (comp % 3);
+            else if (comp < 12) dst = dL_dnormal + gid * 3 + (comp - 9);
+            else dst = dL_dopacity + gid;
+            atomicAdd(dst, sum);
+          }
+        }
+      }
+      __syncwarp();
+    }
+    nent = 0;
+    pending = 0;
+    if (chunk < 0) break;
   }
 #ifdef RENDER_TRACE
   if (lane == 0 && blockIdx.x < 8192) g_btrace[blockIdx.x][1] = btime();
@@ -454,8 +519,12 @@ backward_preprocess_kernel(int P, const int *__restrict__ radii,
 
 void launch_render_backward(const BwdParams &p, const GeomView &g, const ImageView &im,
                             const BinView &b, cudaStream_t s) {
-  render_backward_kernel<<<im.tiles * SUBS_PER_TILE, 32, 0, LS(s)>>>(
-      im.ranges, im.bwd_order, b.point_list, reinterpret_cast<const uint16_t *>(b.hdr), b.hdr, g.rec,
+  static unsigned long long seen = 0;
+  if (first_use_on_device(seen))   // one-warp CTAs with ~10 KB each: residency needs the carve-out
+    cudaFuncSetAttribute(render_backward_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                         cudaSharedmemCarveoutMaxShared);
+  render_backward_kernel<<<im.tiles * UNITS_PER_TILE, 32, 0, LS(s)>>>(
+      im.ranges, im.bwd_order, b.point_list, reinterpret_cast<const char *>(b.hdr), b.hdr, g.rec,
       p.projmatrix, p.W, p.H, im.tiles_x, (uint32_t)p.P, im.final_T, im.n_contrib, p.dL_dout, p.dL_dtransMat, p.dL_dnormal, p.dL_dopacity);
 }
 

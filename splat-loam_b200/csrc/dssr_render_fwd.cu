@@ -49,13 +49,13 @@ struct PixelState {
   bool done;
 };
 
-// forward.cu:302-330 for one surviving (pixel, surfel) pair
-__device__ __forceinline__ void blend(PixelState &p, float alpha, float depth, float nx, float ny,
+// forward.cu:302-330 for one surviving (pixel, surfel) pair; false: the pixel terminated instead
+__device__ __forceinline__ bool blend(PixelState &p, float alpha, float depth, float nx, float ny,
                                       float nz, uint32_t contributor) {
   const float test_T = FM(p.T, FS(1.0f, alpha));
   if (test_T < 0.0001f) {
     p.done = true;
-    return;
+    return false;
   }
   const float w = FM(p.T, alpha);
   const float A = FS(1.0f, p.T);
@@ -75,6 +75,7 @@ __device__ __forceinline__ void blend(PixelState &p, float alpha, float depth, f
   p.N2 = FF(nz, w, p.N2);
   p.T = test_T;
   p.last_contributor = contributor;
+  return true;
 }
 
 // One WARP per CTA = one 4x4 sub-tile.  CTAs are numbered in order of decreasing tile list
@@ -87,7 +88,8 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
                       const float *__restrict__ projmatrix, int W, int H, int tiles_x,
                       uint32_t capacity, uint32_t P, float *__restrict__ final_T,
                       uint32_t *__restrict__ n_contrib, float *__restrict__ out,
-                      uint32_t *__restrict__ sub_cost) {
+                      uint32_t *__restrict__ sub_cost, uint32_t *__restrict__ blend_bits,
+                      uint32_t bits_stride, uint16_t *__restrict__ pix_mask, uint32_t pix_stride) {
   // double-buffered staging ring: while the survivors of one 32-entry step are being
   // composited, the records of the next step's survivors are already in flight
   __shared__ float4 s_rec[2][32][4];
@@ -116,6 +118,12 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
   range.x = min(range.x, capacity);   // only bites when the capacity hint was too small
   range.y = min(range.y, capacity);
   const uint32_t lt = (1u << lane) - 1u;
+  // The record of what was blended, for the backward: one word per 32-entry step (which of its
+  // entries some pixel of this sub-tile blended) and, per such entry, the mask of those pixels.
+  // The backward then composites exactly these (pixel, entry) pairs and tests nothing.
+  uint32_t *step_word = blend_bits + (size_t)sub * bits_stride + (range.x >> 5) + tile;
+  uint16_t *pix = pix_mask + (size_t)sub * pix_stride + range.x;
+  uint32_t step_bits = 0u, npairs = 0u;
 
   PixelState ps;
   ps.T = 1.0f;
@@ -191,18 +199,36 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
       const float alpha_o = __shfl_xor_sync(0xffffffffu, h.alpha, 16);
       const float depth_o = __shfl_xor_sync(0xffffffffu, h.depth, 16);
       const bool ok1 = half ? ok_o : ok, ok2 = half ? ok : ok_o;
+      bool b1 = false, b2 = false;
       if (ok1) {
         const float4 c = s_rec[cur][pair][2];
-        blend(ps, half ? alpha_o : h.alpha, half ? depth_o : h.depth, c.y, c.z, c.w,
-              s_pos[cur][pair]);
+        b1 = blend(ps, half ? alpha_o : h.alpha, half ? depth_o : h.depth, c.y, c.z, c.w,
+                   s_pos[cur][pair]);
       }
       if (ok2 && !ps.done) {
         const float4 c = s_rec[cur][pair + 1][2];
-        blend(ps, half ? h.alpha : alpha_o, half ? h.depth : depth_o, c.y, c.z, c.w,
-              s_pos[cur][pair + 1]);
+        b2 = blend(ps, half ? h.alpha : alpha_o, half ? h.depth : depth_o, c.y, c.z, c.w,
+                   s_pos[cur][pair + 1]);
+      }
+      // (both halves carry the same 16 pixel states: the low half's votes are the pixel mask)
+      const uint32_t m1 = __ballot_sync(0xffffffffu, b1) & 0xffffu;
+      const uint32_t m2 = __ballot_sync(0xffffffffu, b2) & 0xffffu;
+      if (m1) {
+        const uint32_t q = s_pos[cur][pair] - 1u;
+        if (lane == 0) pix[q] = (uint16_t)m1;
+        step_bits |= 1u << (q & 31u);
+        npairs += __popc(m1);
+      }
+      if (m2) {
+        const uint32_t q = s_pos[cur][pair + 1] - 1u;
+        if (lane == 0) pix[q] = (uint16_t)m2;
+        step_bits |= 1u << (q & 31u);
+        npairs += __popc(m2);
       }
       if (__all_sync(0xffffffffu, ps.done)) break;
     }
+    if (lane == 0) step_word[(base - range.x) >> 5] = step_bits;
+    step_bits = 0u;
     // ---- park the next step's records in the other buffer ----
     if (nhit) {
       const int slot = __popc(nm & lt);
@@ -223,14 +249,9 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
     g_rtrace[work][3] = range.y - range.x;
   }
 #endif
-  // what the backward will have to walk for this sub-tile: up to the furthest entry any of its
-  // pixels blended (its CTAs are numbered by decreasing cost, see bwd_order_kernel)
-  {
-    uint32_t far = ps.last_contributor;
-#pragma unroll
-    for (int o = 8; o > 0; o >>= 1) far = max(far, __shfl_xor_sync(0xffffffffu, far, o));
-    if (lane == 0) sub_cost[tile * SUBS_PER_TILE + sub] = far;
-  }
+  // what the backward will have to do for this sub-tile: the number of blended (pixel, entry)
+  // pairs (its warps are numbered by decreasing cost, see bwd_order_kernel)
+  if (lane == 0) sub_cost[tile * SUBS_PER_TILE + sub] = npairs;
   if (inside && half == 0) {
     const size_t HW = (size_t)W * H;
     const size_t pix = (size_t)py * W + px;
@@ -249,11 +270,10 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
   }
 }
 
-// bwd_order[rank] = sub-tile, by decreasing cost (counting sort on cost / 16, one CTA).  The
-// backward's warps run in more than one wave (128 registers: 16 per SM); their run time follows
-// the number of entries they walk (correlation 0.85, against 0.35 for the tile's list length),
-// so longest-first numbering packs the waves: list scheduling of the measured warp times gave
-// 363 us against 618 us for the tile-length order.
+// bwd_order[rank] = backward work unit (two horizontally adjacent sub-tiles = 8x4 pixels, unit
+// u = sub-tiles 2u and 2u+1), by decreasing cost = blended pairs (counting sort on cost / 32,
+// one CTA).  On large images the backward's warps run in more than one wave; longest-first
+// numbering packs the waves.
 // Blocks 1.. of the same launch zero the backward's accumulation buffers (`fill`: four float
 // arrays) meanwhile: one launch instead of fills and a kernel one after the other.
 constexpr int COST_BINS = 2048;
@@ -286,7 +306,8 @@ bwd_order_kernel(const uint32_t *__restrict__ sub_cost, int units, uint32_t *__r
   for (int b = tid; b < COST_BINS; b += 1024) s_bin[b] = 0u;
   __syncthreads();
   for (int u = tid; u < units; u += 1024)
-    atomicAdd(&s_bin[COST_BINS - 1 - min(sub_cost[u] >> 4, (uint32_t)COST_BINS - 1u)], 1u);
+    atomicAdd(&s_bin[COST_BINS - 1 - min((sub_cost[2 * u] + sub_cost[2 * u + 1]) >> 5,
+                                         (uint32_t)COST_BINS - 1u)], 1u);
   __syncthreads();
   // exclusive scan, two bins per thread
   const uint32_t v0 = s_bin[2 * tid], v1 = s_bin[2 * tid + 1];
@@ -305,15 +326,15 @@ bwd_order_kernel(const uint32_t *__restrict__ sub_cost, int units, uint32_t *__r
   s_bin[2 * tid + 1] = before + inc - v1;
   __syncthreads();
   for (int u = tid; u < units; u += 1024)
-    order[atomicAdd(&s_bin[COST_BINS - 1 - min(sub_cost[u] >> 4, (uint32_t)COST_BINS - 1u)], 1u)] =
-        (uint32_t)u;
+    order[atomicAdd(&s_bin[COST_BINS - 1 - min((sub_cost[2 * u] + sub_cost[2 * u + 1]) >> 5,
+                                               (uint32_t)COST_BINS - 1u)], 1u)] = (uint32_t)u;
 }
 
 }  // namespace
 
 void launch_bwd_order(const ImageView &im, const FillList &fill, cudaStream_t s) {
   bwd_order_kernel<<<1 + 2 * splat_sm_count(), 1024, 0, LS(s)>>>(
-      im.sub_cost, im.tiles * SUBS_PER_TILE, im.bwd_order, fill);
+      im.sub_cost, im.tiles * SUBS_PER_TILE / 2, im.bwd_order, fill);
 }
 
 void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageView &im,
@@ -325,5 +346,6 @@ void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageVie
                          cudaSharedmemCarveoutMaxShared);
   render_forward_kernel<<<im.tiles * SUBS_PER_TILE, 32, 0, LS(s)>>>(
       im.ranges, order, b.point_list, b.sub_mask, g.rec, p.projmatrix, p.W, p.H, im.tiles_x,
-      capacity, (uint32_t)p.P, im.final_T, im.n_contrib, p.out_maps, im.sub_cost);
+      capacity, (uint32_t)p.P, im.final_T, im.n_contrib, p.out_maps, im.sub_cost, b.blend_bits,
+      b.bits_stride, b.pix_mask, b.pix_stride);
 }

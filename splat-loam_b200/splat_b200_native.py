@@ -114,9 +114,11 @@ EXPORTS = (
     "splat_xchg_push", "splat_xchg_reduce", "splat_xchg_wait", "splat_xchg_allreduce",
     "splat_xchg_result", "splat_xchg_destroy", "dssr_post_forward", "dssr_post_backward",
     "dssr_post_loss_forward", "dssr_post_loss_backward", "splat_activation_adam_step",
-    "splat_xchg_fault", "splat_launch_count",
+    "splat_xchg_fault", "splat_launch_count", "splat_compact_workspace_bytes",
+    "splat_compact_plan", "splat_compact_rows", "splat_append_rows",
 )
 XCHG_HANDLE_BYTES = 64
+SURGERY_MAX_TENSORS = 12
 
 _lib = None
 
@@ -191,6 +193,16 @@ def load():
     lib.splat_xchg_destroy.argtypes = [vp]
     lib.splat_xchg_fault.argtypes = [vp]
     lib.splat_xchg_fault.restype = ctypes.c_int
+    pp = ctypes.POINTER(ctypes.c_void_p)
+    ip = ctypes.POINTER(ctypes.c_int)
+    lib.splat_compact_workspace_bytes.argtypes = [ctypes.c_int]
+    lib.splat_compact_workspace_bytes.restype = ctypes.c_size_t
+    lib.splat_compact_plan.argtypes = [ctypes.c_int, vp, vp, ip, vp]
+    lib.splat_compact_plan.restype = ctypes.c_int
+    lib.splat_compact_rows.argtypes = [ctypes.c_int, vp, vp, ctypes.c_int, pp, pp, ip, vp]
+    lib.splat_compact_rows.restype = ctypes.c_int
+    lib.splat_append_rows.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, pp, pp, pp, ip, vp]
+    lib.splat_append_rows.restype = ctypes.c_int
     lib.splat_launch_count.argtypes = []
     lib.splat_launch_count.restype = ctypes.c_ulonglong
     for f in (lib.splat_xchg_create, lib.splat_xchg_export, lib.splat_xchg_connect,
