@@ -338,6 +338,50 @@ SPLAT_API int splat_append_rows(int n_old, int n_new, int ntensors, const float 
                                 const float *const *ext, float *const *dst, const int *width,
                                 void *stream);
 
+/* ---- photometric (range-image) registration -------------------------------------------
+ * Replaces the photometric stage of the reference's gsaligner submodule as Splat-LOAM's
+ * tracker drives it (slam/tracker.py:160-188 -> GSAligner::setReference / setQuery /
+ * alignPhotometric, submodules/gsaligner/gsaligner/aligner.cu:181-258,329-342 ->
+ * photo::PhotometricFac::compute, registration/photometric.cpp:55-77 and
+ * registration/photometric_cuda.cu:8-395; image preparation tools/image_set_impl.cu:20-120,
+ * 254-376): spherical camera, depth channel, identity sensor offset.
+ *   gsa_photo_workspace_bytes  size of the caller-owned device workspace for an H x W image;
+ *   gsa_photo_set_reference    reference range image (device, [H*W], > 1e-5 = measured):
+ *                              mask, mask growing by `mask_grow_radius`, clamped central
+ *                              differences (threshold `depth_derivative_threshold`);
+ *   gsa_photo_set_query        query range image -> point cloud in the sensor frame;
+ *   gsa_photo_align            `iterations` Gauss-Newton steps from `initial_guess` (HOST,
+ *                              row-major 4x4 ref_T_query): per step one z-buffer projection and
+ *                              one linearise + reduce + solve kernel, pose kept on the device,
+ *                              no host round trip in between.  Outputs (HOST): transform
+ *                              (row-major 4x4), stats = {residual, inlier ratio} as
+ *                              PhotometricFac::compute returns them, and optionally `system`
+ *                              = the sums of the LAST linearisation: upper triangle of H (21,
+ *                              row by row) | b (6) | chi | good | inliers.  Synchronises
+ *                              `stream` before it returns. */
+typedef struct {
+  int H, W;
+  float fx, fy, cx, cy;               /* spherical camera matrix K (projmatrix[:3,:3]^T)  */
+  float min_depth, max_depth;         /* photo_min_depth, photo_max_depth                 */
+  float omega_depth;                  /* photo_omega_depth                                */
+  float depth_rejection_threshold;    /* photo_depth_rejection_threshold                  */
+  float kernel_chi_threshold;         /* photo_rho_kernel                                 */
+  void *stream;
+} gsa_photo_params;
+SPLAT_API size_t gsa_photo_workspace_bytes(int H, int W);
+SPLAT_API int gsa_photo_set_reference(void *workspace, int H, int W, const float *depth,
+                                      float depth_derivative_threshold, int mask_grow_radius,
+                                      void *stream);
+SPLAT_API int gsa_photo_set_query(void *workspace, int H, int W, const float *depth, float fx,
+                                  float fy, float cx, float cy, float min_depth, float max_depth,
+                                  void *stream);
+/* parity-test accessor: the prepared reference image as four [H*W] float planes on the
+ * device: depth | d/dcol | d/drow | masked (1 / 0) */
+SPLAT_API int gsa_photo_debug_reference(void *workspace, int H, int W, float *out, void *stream);
+SPLAT_API int gsa_photo_align(void *workspace, const gsa_photo_params *p,
+                              const float *initial_guess, int iterations, float *transform,
+                              float *stats, double *system);
+
 /* Number of kernels this library has launched so far in this process (all threads, all
  * devices).  No counterpart in the reference.  A harness takes the difference around a timed
  * region to report how many of the library's kernels ran in it. */

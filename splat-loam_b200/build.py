@@ -17,12 +17,14 @@ SOURCES = [
     "dssr_preprocess.cu",
     "radix_sort.cu",
     "dssr_render_fwd.cu",
+    "dssr_render_fwd_steps.cu",
     "dssr_render_bwd.cu",
     "sknn.cu",
     "peer_exchange.cu",
     "render_post.cu",
     "adam_step.cu",
     "state_surgery.cu",
+    "photometric.cu",
 ]
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-lineinfo",

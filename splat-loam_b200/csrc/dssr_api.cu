@@ -157,7 +157,9 @@ int run_binning_and_render(const dssr_forward_args *a, const FwdParams &fp,
   LAUNCH_CHECK(dbg, st, "sort");
   {
     ProfScope ps("render_forward", st);
-    launch_render_forward(fp, gv, iv, bv, capacity, st);
+    static const bool steps = getenv("SPLAT_B200_FWD") && !strcmp(getenv("SPLAT_B200_FWD"), "steps");
+    if (steps) launch_render_forward_steps(fp, gv, iv, bv, capacity, st);
+    else launch_render_forward(fp, gv, iv, bv, capacity, st);
   }
   LAUNCH_CHECK(dbg, st, "render_forward");
   return 0;

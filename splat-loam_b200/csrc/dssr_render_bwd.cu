@@ -47,6 +47,7 @@ constexpr int SUBS_PER_TILE = (SPLAT_TILE / SUB) * (SPLAT_TILE / SUB);   // 16
 constexpr int UNITS_PER_TILE = SUBS_PER_TILE / 2;                 // a warp = two sub-tiles
 constexpr int ENT_CAP = 64;        // blended entries staged per warp
 constexpr int GATHER_PAIRS = 64;   // entries are gathered until they hold this many pairs
+constexpr int QUEUE_CAP = GATHER_PAIRS + 32 * 32;   // one more step can add 32 entries x 32 pixels
 
 // Per-pixel state of the reverse traversal (backward.cu:62-98) and its constants.
 struct BackState {
@@ -93,17 +94,6 @@ __device__ __forceinline__ StepOut recur(BackState &b, const PixelConst &c, floa
   return o;
 }
 
-// position of the k-th (0-based) set bit of m (k < popc(m))
-__device__ __forceinline__ uint32_t select_bit(uint32_t m, uint32_t k) {
-  uint32_t pos = 0, c;
-  c = __popc(m & 0xffffu); if (k >= c) { pos = 16; k -= c; m >>= 16; }
-  c = __popc(m & 0xffu);   if (k >= c) { pos += 8; k -= c; m >>= 8; }
-  c = __popc(m & 0xfu);    if (k >= c) { pos += 4; k -= c; m >>= 4; }
-  c = __popc(m & 0x3u);    if (k >= c) { pos += 2; k -= c; m >>= 2; }
-  c = m & 1u;              if (k >= c) { pos += 1; }
-  return pos;
-}
-
 // everything a warp stages in shared memory (one warp per CTA)
 struct __align__(16) WarpStage {
   float4 rec[ENT_CAP][4];           // the gathered entries' 64-byte records
@@ -118,6 +108,7 @@ struct __align__(16) WarpStage {
   uint32_t pe[32];                  // P1 -> P2: entry slot of the pair
   uint32_t pmask[32];               // per pixel: which lanes of the batch hold its pairs
   float vbuf[32][13];               // P3: the pairs' 13 contributions, summed per entry
+  uint16_t queue[QUEUE_CAP];        // the gathered pairs, (slot << 5) | pixel, back to front
 };
 
 // One WARP per CTA = one 8x4 pixel block; CTAs in order of decreasing number of pairs.
@@ -206,8 +197,38 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
 
   const int top_a = max_a ? (int)((max_a - 1) >> 5) : -1, top_b = max_b ? (int)((max_b - 1) >> 5) : -1;
   int chunk = (int)((max_last - 1) >> 5);
-  // the step words run one step ahead of their use
-  uint32_t nword_a = chunk <= top_a ? words_a[chunk] : 0u, nword_b = chunk <= top_b ? words_b[chunk] : 0u;
+  const uint32_t lt = (1u << lane) - 1u;
+  // Software pipeline of the walk (back to front): the step words are fetched three steps
+  // ahead of their use, the blended entries' surfel indices and pixel masks two steps ahead,
+  // their records one step ahead (into registers) - each load's L2 latency sits under the
+  // work on the steps before it.
+  auto load_words = [&](int c, uint32_t &wa, uint32_t &wb) {
+    wa = (c >= 0 && c <= top_a) ? words_a[c] : 0u;
+    wb = (c >= 0 && c <= top_b) ? words_b[c] : 0u;
+  };
+  auto load_entry = [&](int c, uint32_t wa, uint32_t wb, uint32_t &id, uint32_t &mask) {
+    id = 0u;
+    mask = 0u;
+    if (((wa | wb) >> lane) & 1u) {
+      const uint32_t q = ((uint32_t)c << 5) + lane;
+      id = min(plist[q], P - 1u);
+      if ((wa >> lane) & 1u) mask = pm_a[q];
+      if ((wb >> lane) & 1u) mask |= (uint32_t)pm_b[q] << 16;
+    }
+  };
+  uint32_t w0a, w0b, w1a, w1b, w2a, w2b;           // words of chunk, chunk - 1, chunk - 2
+  load_words(chunk, w0a, w0b);
+  load_words(chunk - 1, w1a, w1b);
+  load_words(chunk - 2, w2a, w2b);
+  uint32_t id0, mask0, id1, mask1;                  // entries of chunk, chunk - 1
+  load_entry(chunk, w0a, w0b, id0, mask0);
+  load_entry(chunk - 1, w1a, w1b, id1, mask1);
+  float4 ra, rb, rc, rd;                            // records of chunk
+  ra = rb = rc = rd = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (mask0) {
+    const float4 *r = rec + 4 * (size_t)id0;
+    ra = __ldg(r); rb = __ldg(r + 1); rc = __ldg(r + 2); rd = __ldg(r + 3);
+  }
   int nent = 0;
   uint32_t pending = 0;
   __syncwarp();
@@ -215,45 +236,38 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
   while (true) {
     // ---- gather blended entries, back to front, until they hold enough pairs ----
     while (chunk >= 0 && pending < GATHER_PAIRS && nent + 32 <= ENT_CAP) {
-      const uint32_t word_a = nword_a, word_b = nword_b;
-      if (chunk >= 1) {
-        nword_a = chunk - 1 <= top_a ? words_a[chunk - 1] : 0u;
-        nword_b = chunk - 1 <= top_b ? words_b[chunk - 1] : 0u;
+      const uint32_t vote = w0a | w0b;
+      const uint32_t id = id0, mask = mask0;
+      const float4 a = ra, b = rb, c = rc, d = rd;
+      // advance the pipeline
+      w0a = w1a; w0b = w1b; w1a = w2a; w1b = w2b;
+      load_words(chunk - 3, w2a, w2b);
+      id0 = id1; mask0 = mask1;
+      load_entry(chunk - 2, w1a, w1b, id1, mask1);
+      if (mask0) {
+        const float4 *r = rec + 4 * (size_t)id0;
+        ra = __ldg(r); rb = __ldg(r + 1); rc = __ldg(r + 2); rd = __ldg(r + 3);
       }
-      const uint32_t vote = word_a | word_b;
       if (vote) {
-        const bool in_a = (word_a >> lane) & 1u, in_b = (word_b >> lane) & 1u;
-        const bool any = in_a || in_b;
-        const uint32_t q = ((uint32_t)chunk << 5) + lane;
-        uint32_t mask = 0u, id = 0u;
-        if (any) {
-          id = min(plist[q], P - 1u);
-          if (in_a) mask = pm_a[q];
-          if (in_b) mask |= (uint32_t)pm_b[q] << 16;
-        }
-        float4 ra, rb, rc, rd;
-        if (any) {
-          const float4 *r = rec + 4 * (size_t)id;
-          ra = __ldg(r); rb = __ldg(r + 1); rc = __ldg(r + 2); rd = __ldg(r + 3);
-        }
-        const uint32_t cnt = __popc(mask);
-        uint32_t suffix = cnt;                    // pairs of this lane's entry and of all later ones
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const uint32_t n = __shfl_down_sync(full, suffix, o);
-          if (lane + o < 32) suffix += n;
-        }
-        const uint32_t total = __shfl_sync(full, suffix, 0);
+        const bool any = (vote >> lane) & 1u;
+        const int ns = __popc(vote);
         if (any) {
           const int slot = nent + __popc(vote >> lane) - 1;     // later entries first
           st.ent_id[slot] = id;
-          st.ent_pos[slot] = q;
+          st.ent_pos[slot] = ((uint32_t)chunk << 5) + lane;
           st.ent_mask[slot] = mask;
-          st.ent_prefix[slot] = pending + suffix - cnt;
-          st.rec[slot][0] = ra; st.rec[slot][1] = rb; st.rec[slot][2] = rc; st.rec[slot][3] = rd;
+          st.rec[slot][0] = a; st.rec[slot][1] = b; st.rec[slot][2] = c; st.rec[slot][3] = d;
         }
-        nent += __popc(vote);
-        pending += total;
+        __syncwarp();
+        // lay the entries' pairs end to end: every pixel's lane appends itself
+        for (int k = 0; k < ns; k++) {
+          const int slot = nent + k;
+          const uint32_t m = st.ent_mask[slot];
+          if (lane == 0) st.ent_prefix[slot] = pending;
+          if ((m >> lane) & 1u) st.queue[pending + __popc(m & lt)] = (uint16_t)((slot << 5) | lane);
+          pending += __popc(m);
+        }
+        nent += ns;
       }
       chunk--;
     }
@@ -268,15 +282,9 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
     for (uint32_t base = 0; base < pending; base += 32) {
       const uint32_t g = base + lane;
       const bool valid = g < pending;
-      // P1: which (entry, pixel) is pair g?  binary search over the prefix sums
-      int j = 0;
-#pragma unroll
-      for (int s = ENT_CAP / 2; s > 0; s >>= 1) {
-        const int j2 = j + s;
-        if (j2 < nent && st.ent_prefix[j2] <= g) j = j2;
-      }
-      const uint32_t emask = st.ent_mask[j];
-      const int pixel = valid ? (int)select_bit(emask, g - st.ent_prefix[j]) : lane;
+      // P1: pair g of the queue: intersection, alpha, depth
+      const uint32_t item = valid ? st.queue[g] : (uint32_t)lane;
+      const int j = item >> 5, pixel = item & 31;
       const SurfelRec s = unpack_rec(st.rec[j][0], st.rec[j][1], st.rec[j][2], st.rec[j][3]);
       PixelRay ray;
       ray.X = st.ray[0][pixel];  ray.Y = st.ray[1][pixel];  ray.Z = st.ray[2][pixel];
@@ -284,18 +292,14 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
       ray.ex = st.ray[5][pixel]; ray.ey = st.ray[6][pixel]; ray.ez = st.ray[7][pixel];
       ray.pxf = st.ray[8][pixel]; ray.pyf = st.ray[9][pixel];
       Hit h;
-      intersect_begin(ray, s, 3.0e38f, h);
       // the forward blended this pair, so the same arithmetic passes the same tests
-      const bool ok = valid && intersect_finish(ray, s, h);
+      const bool ok = intersect_all(ray, s, h) && valid;
       st.pa[lane] = h.alpha;
       st.pd[lane] = h.depth;
       st.pe[lane] = (uint32_t)j;
       st.pmask[lane] = 0u;
       __syncwarp();
-      {
-        const uint32_t peers = __match_any_sync(full, ok ? pixel : 64 + lane);
-        if (ok) st.pmask[pixel] = peers;
-      }
+      if (ok) atomicOr(&st.pmask[pixel], 1u << lane);
       __syncwarp();
       // P2: every pixel's lane runs its recurrences over its pairs of the batch, in list order
       {
@@ -380,8 +384,14 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
           const int e = j_first + seg;
           const int q0 = max((int)st.ent_prefix[e] - (int)base, 0);
           const int q1 = min((int)st.ent_prefix[e + 1] - (int)base, nvalid);
-          float sum = 0.0f;
-          for (int q = q0; q < q1; q++) sum += st.vbuf[q][comp];
+          float s0 = 0.0f, s1 = 0.0f;
+          int q = q0;
+          for (; q + 1 < q1; q += 2) {
+            s0 += st.vbuf[q][comp];
+            s1 += st.vbuf[q + 1][comp];
+          }
+          if (q < q1) s0 += st.vbuf[q][comp];
+          const float sum = s0 + s1;
           if (sum != 0.0f) {
             const size_t gid = st.ent_id[e];
             float *dst;

@@ -3,23 +3,26 @@
 // Replaces renderCUDA<3>, submodules/diff-surfel-spherical-rasterization/
 // cuda_rasterizer/forward.cu:172-351 (launch :353-362).
 //
-// The reference runs one 256-thread CTA per 16x16 tile; every pixel walks the tile's
-// whole depth-sorted list and the CTA leaves only when all 256 pixels are done.  On a
-// 64x1024 range image that is 256 CTAs on 148 SMs, and a warp's dependent-instruction
-// chain is as long as the tile's list.  Here the unit of work is a WARP that owns a 4x4
-// pixel sub-tile (4096 warps at 64x1024) and walks its tile's list on its own:
-//   * 32 list entries per step: each lane reads its entry's 16-bit sub-tile mask (written
-//     by the last sort pass from the surfel's conservative cull box) and a ballot compacts
-//     the entries that can touch this sub-tile; their 64-byte records are gathered
-//     (128-bit loads, L2-resident) into a warp-private shared-memory ring;
-//   * survivors are evaluated TWO AT A TIME: lanes 0-15 intersect the 16 pixels with one
-//     surfel, lanes 16-31 with the next; the results are swapped by shuffle and both
-//     halves blend both surfels in list order, so every lane carries its pixel's state;
-//   * the warp stops as soon as ITS 16 pixels are done.
-// Skipping an entry whose cull box misses the sub-tile is exact: such an entry fails the
-// reference's alpha >= 1/255 test at every pixel of the sub-tile, i.e. it is one the
-// reference `continue`s over without touching any state.  `contributor` keeps counting
-// list positions, so n_contrib / median_contributor are the reference's.
+// The reference runs one 256-thread CTA per 16x16 tile; every pixel walks the tile's whole
+// depth-sorted list, evaluates every entry and the CTA leaves only when all 256 pixels are
+// done.  Here the unit of work is a WARP that owns an 8x4 pixel block (two 4x4 sub-tiles) and
+// walks its tile's list on its own, in three stages that each keep the 32 lanes busy:
+//   * gather: 32 list entries per step; the entries whose 16-bit sub-tile mask (written by the
+//     last sort pass from the surfel's conservative cull box) touches the block are staged in
+//     shared memory - 64-byte record and 16-byte cull box, 128-bit loads, L2-resident - and
+//     every pixel tests itself against each staged entry's cull box; the (pixel, entry) pairs
+//     that pass are appended to a queue, in list order;
+//   * evaluate: the queue is consumed 32 pairs at a time, ONE PAIR PER LANE whatever its pixel
+//     and entry: ray-splat intersection, alpha, depth (forward.cu:249-301);
+//   * blend: every pixel's own lane blends its pairs of the batch in list order
+//     (forward.cu:302-330), with early termination; the warp stops when its 32 pixels are done.
+// Skipping a pair whose pixel lies outside the entry's cull box is exact: the box bounds where
+// alpha >= 1/255 is possible, so such a pair is one the reference `continue`s over without
+// touching any state.  `contributor` keeps counting list positions, so n_contrib /
+// median_contributor are the reference's.
+// The kernel also writes down what it blended - per 32-entry step one word per sub-tile (which
+// entries) and per blended entry the 16-bit mask of the sub-tile's pixels - which is all the
+// backward needs to know (dssr_render_bwd.cu).
 #include "raster_math.cuh"
 
 #ifdef RENDER_TRACE
@@ -34,14 +37,15 @@ __device__ __forceinline__ unsigned long long rtime() {
 }
 #endif
 
-#ifndef FWD_WARPS_PER_SM
-#define FWD_WARPS_PER_SM 28
-#endif
-
 namespace {
 
-constexpr int SUB = 4;                                            // 4x4 pixels per warp
+constexpr int SUB = 4;                                            // 4x4 pixels per sub-tile
 constexpr int SUBS_PER_TILE = (SPLAT_TILE / SUB) * (SPLAT_TILE / SUB);   // 16
+constexpr int UNITS_PER_TILE = SUBS_PER_TILE / 2;                 // a warp = two sub-tiles
+constexpr int ENT_CAP = 64;        // entries staged per gather phase
+constexpr int STEP_CAP = 8;        // 32-entry steps per gather phase
+constexpr int GATHER_PAIRS = 64;   // a phase is evaluated once it holds this many pairs
+constexpr int QUEUE_CAP = GATHER_PAIRS + 32 * 32;   // one more step can add 32 entries x 32 pixels
 
 struct PixelState {
   float T, D, N0, N1, N2, M1, M2, dist, median_depth;
@@ -78,166 +82,256 @@ __device__ __forceinline__ bool blend(PixelState &p, float alpha, float depth, f
   return true;
 }
 
-// One WARP per CTA = one 4x4 sub-tile.  CTAs are numbered in order of decreasing tile list
-// length (tile_order), so the hardware's round-robin placement hands every SM a balanced
-// mix of long and short lists.
-__global__ void __launch_bounds__(32, FWD_WARPS_PER_SM)
+// everything a warp stages in shared memory (one warp per CTA)
+struct __align__(16) FwdStage {
+  float4 rec[ENT_CAP][4];        // the staged entries' 64-byte records
+  float4 cull[ENT_CAP];          // and cull boxes
+  float cut[ENT_CAP];            // conservative cutoff on rho for the entry's opacity
+  uint32_t ent_pos[ENT_CAP];     // the reference's `contributor` (1-based list position)
+  uint32_t ent_mask[ENT_CAP];    // pixels that blended the entry (bit = lane of the pixel)
+  uint32_t word_a[STEP_CAP], word_b[STEP_CAP];   // the phase's step words, per sub-tile
+  float ray[10][32];             // per pixel: X Y Z ax ay ex ey ez pxf pyf
+  float pa[32], pd[32];          // evaluate -> blend: alpha (0: the pair failed), depth
+  uint32_t pe[32];               // evaluate -> blend: entry slot of the pair
+  uint32_t pmask[32];            // per pixel: which lanes of the batch hold its pairs
+  uint16_t queue[QUEUE_CAP];     // (slot << 5) | pixel, in list order
+};
+
+// One WARP per CTA = one 8x4 pixel block.  CTAs are numbered in order of decreasing tile list
+// length (tile_order), so the hardware's round-robin placement hands every SM a balanced mix
+// of long and short lists.
+__global__ void __launch_bounds__(32, 16)
 render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restrict__ tile_order,
                       const uint32_t *__restrict__ point_list,
                       const uint16_t *__restrict__ sub_mask, const float4 *__restrict__ rec,
-                      const float *__restrict__ projmatrix, int W, int H, int tiles_x,
-                      uint32_t capacity, uint32_t P, float *__restrict__ final_T,
-                      uint32_t *__restrict__ n_contrib, float *__restrict__ out,
-                      uint32_t *__restrict__ sub_cost, uint32_t *__restrict__ blend_bits,
-                      uint32_t bits_stride, uint16_t *__restrict__ pix_mask, uint32_t pix_stride) {
-  // double-buffered staging ring: while the survivors of one 32-entry step are being
-  // composited, the records of the next step's survivors are already in flight
-  __shared__ float4 s_rec[2][32][4];
-  __shared__ float s_cut[2][32];
-  __shared__ uint32_t s_pos[2][32];
+                      const float4 *__restrict__ cull, const float *__restrict__ projmatrix, int W,
+                      int H, int tiles_x, uint32_t capacity, uint32_t P,
+                      float *__restrict__ final_T, uint32_t *__restrict__ n_contrib,
+                      float *__restrict__ out, uint32_t *__restrict__ unit_cost,
+                      uint32_t *__restrict__ blend_bits, uint32_t bits_stride,
+                      uint16_t *__restrict__ pix_mask, uint32_t pix_stride) {
+  __shared__ FwdStage st;
   const int lane = threadIdx.x, half = lane >> 4, p16 = lane & 15;
+  const uint32_t full = 0xffffffffu;
   const uint32_t work = blockIdx.x;
 #ifdef RENDER_TRACE
   const unsigned long long t_start = rtime();
   uint32_t n_steps = 0, n_pairs = 0;
 #endif
-  const uint32_t tile = tile_order ? tile_order[work / SUBS_PER_TILE] : work / SUBS_PER_TILE;
-  const int sub = work % SUBS_PER_TILE;
-  const int x0 = (tile % tiles_x) * SPLAT_TILE + (sub & 3) * SUB;
-  const int y0 = (tile / tiles_x) * SPLAT_TILE + (sub >> 2) * SUB;
+  const uint32_t tile = tile_order ? tile_order[work / UNITS_PER_TILE] : work / UNITS_PER_TILE;
+  const int unit = work % UNITS_PER_TILE;
+  const int sub_a = 2 * unit;                                   // left sub-tile; right = sub_a + 1
+  const int x0 = (tile % tiles_x) * SPLAT_TILE + (sub_a & 3) * SUB;
+  const int y0 = (tile / tiles_x) * SPLAT_TILE + (sub_a >> 2) * SUB;
   if (x0 >= W || y0 >= H) {
-    if (lane == 0) sub_cost[tile * SUBS_PER_TILE + sub] = 0u;
+    if (lane == 0) unit_cost[tile * UNITS_PER_TILE + unit] = 0u;
     return;
   }
-  const int px = x0 + (p16 & 3), py = y0 + (p16 >> 2);
+  const int px = x0 + SUB * half + (p16 & 3), py = y0 + (p16 >> 2);
   const bool inside = px < W && py < H;
   const float fx = projmatrix[0], fy = projmatrix[5], cx = projmatrix[8], cy = projmatrix[9];
-  const PixelRay ray = make_ray((float)px, (float)py, fx, fy, cx, cy);
+  const float pxf = (float)px, pyf = (float)py;
+  {
+    const PixelRay r = make_ray(pxf, pyf, fx, fy, cx, cy);
+    st.ray[0][lane] = r.X;  st.ray[1][lane] = r.Y;  st.ray[2][lane] = r.Z;
+    st.ray[3][lane] = r.ax; st.ray[4][lane] = r.ay;
+    st.ray[5][lane] = r.ex; st.ray[6][lane] = r.ey; st.ray[7][lane] = r.ez;
+    st.ray[8][lane] = r.pxf; st.ray[9][lane] = r.pyf;
+  }
+  // the cull boxes are only meaningful while |elevation| < pi/2 on every image row (the last
+  // sort pass sets every mask bit otherwise, radix_sort.cu)
+  const float period = 6.2831853f * fabsf(fx);
+  const float inv_period = 1.0f / period;
+  const bool cull_on =
+      fmaxf(fabsf((0.0f - cy) / fy), fabsf(((float)(H - 1) - cy) / fy)) < 1.55f;
 
   uint2 range = ranges[tile];
   range.x = min(range.x, capacity);   // only bites when the capacity hint was too small
   range.y = min(range.y, capacity);
+  const uint32_t len = range.y - range.x;
+  const uint32_t umask = 3u << sub_a;                           // the block's two mask bits
   const uint32_t lt = (1u << lane) - 1u;
-  // The record of what was blended, for the backward: one word per 32-entry step (which of its
-  // entries some pixel of this sub-tile blended) and, per such entry, the mask of those pixels.
-  // The backward then composites exactly these (pixel, entry) pairs and tests nothing.
-  uint32_t *step_word = blend_bits + (size_t)sub * bits_stride + (range.x >> 5) + tile;
-  uint16_t *pix = pix_mask + (size_t)sub * pix_stride + range.x;
-  uint32_t step_bits = 0u, npairs = 0u;
+  // what the backward reads (see the header comment); a step word of this tile's step k lives
+  // at (range.x >> 5) + tile + k, unique per (tile, step)
+  uint32_t *words_a = blend_bits + (size_t)sub_a * bits_stride + (range.x >> 5) + tile;
+  uint32_t *words_b = words_a + bits_stride;
+  uint16_t *pix_a = pix_mask + (size_t)sub_a * pix_stride + range.x;
+  uint16_t *pix_b = pix_a + pix_stride;
+  const uint32_t *plist = point_list + range.x;
+  const uint16_t *smask = sub_mask + range.x;
 
   PixelState ps;
   ps.T = 1.0f;
   ps.D = ps.N0 = ps.N1 = ps.N2 = ps.M1 = ps.M2 = ps.dist = ps.median_depth = 0.0f;
   ps.last_contributor = ps.median_contributor = 0;
   ps.done = !inside;
+  uint32_t npairs = 0;
 
-  // ---- prologue: stage step 0, fetch the masks of step 1 ----
-  uint32_t m;   // survivors of the step about to be composited (staged in buffer `cur`)
-  {
-    const uint32_t i0 = range.x + lane;
-    const bool hit = (i0 < range.y) && ((sub_mask[i0] >> sub) & 1u);
-    m = __ballot_sync(0xffffffffu, hit);
-    if (hit) {
-      const int slot = __popc(m & lt);
-      // (id < P only fails on the garbage a too-small capacity hint leaves behind; that
-      // frame is re-run with the exact size)
-      const uint32_t id = min(point_list[i0], P - 1u);
-      const float4 *r = rec + 4 * (size_t)id;
-      const float4 a = __ldg(r), b = __ldg(r + 1), c = __ldg(r + 2), d = __ldg(r + 3);
-      s_rec[0][slot][0] = a; s_rec[0][slot][1] = b; s_rec[0][slot][2] = c; s_rec[0][slot][3] = d;
-      s_cut[0][slot] = rho_cutoff(d.x);
-      s_pos[0][slot] = lane + 1;   // the reference's `contributor`
-    }
+  const uint32_t nsteps = (len + 31) >> 5;
+  uint32_t step = 0;
+  // Software pipeline of the walk: masks and surfel indices are fetched two steps ahead of
+  // their use, the records and cull boxes of a step's entries one step ahead (into registers),
+  // so that their L2 latency sits under the previous step's tests and the evaluation phase.
+  uint32_t cmask = 0u, cid = 0u, nmask = 0u, nid = 0u;
+  if (lane < len) {
+    cmask = smask[lane];
+    cid = plist[lane];
   }
-  // masks and surfel indices run two steps ahead, records one step ahead
-  uint32_t nmask = 0u, nid = 0u;
-  if (range.x + 32 + lane < range.y) {
-    nmask = sub_mask[range.x + 32 + lane];
-    nid = point_list[range.x + 32 + lane];
+  if (32 + lane < len) {
+    nmask = smask[32 + lane];
+    nid = plist[32 + lane];
+  }
+  float4 ra, rb, rc, rd, rcb;
+  ra = rb = rc = rd = rcb = make_float4(0.f, 0.f, 0.f, 0.f);
+  if ((cmask & umask) != 0u) {
+    // (id < P only fails on the garbage a too-small capacity hint leaves behind; that frame is
+    // re-run with the exact size)
+    const uint32_t id = min(cid, P - 1u);
+    const float4 *r = rec + 4 * (size_t)id;
+    ra = __ldg(r); rb = __ldg(r + 1); rc = __ldg(r + 2); rd = __ldg(r + 3);
+    rcb = __ldg(cull + id);
   }
   __syncwarp();
-  int cur = 0;
-  for (uint32_t base = range.x; base < range.y; base += 32, cur ^= 1) {
-    if (__all_sync(0xffffffffu, ps.done)) break;
-    // ---- issue the loads of the NEXT step (consumed after this step's compositing) ----
-    const bool nhit = (nmask >> sub) & 1u;
-    const uint32_t nm = __ballot_sync(0xffffffffu, nhit);
-    const uint32_t id1 = min(nid, P - 1u);
-    {
-      const uint32_t ni = base + 64 + lane;
-      nmask = 0u;
-      if (ni < range.y) {
-        nmask = sub_mask[ni];
-        nid = point_list[ni];
+
+  while (step < nsteps && !__all_sync(full, ps.done)) {
+    // ---- gather: stage the entries that can touch the block, queue the candidate pairs ----
+    int nent = 0, gsteps = 0;
+    uint32_t pending = 0;
+    const uint32_t step0 = step;
+    while (step < nsteps && pending < GATHER_PAIRS && nent + 32 <= ENT_CAP && gsteps < STEP_CAP) {
+      const bool hit = (cmask & umask) != 0u;
+      const uint32_t vote = __ballot_sync(full, hit);
+      const float4 a = ra, b = rb, c = rc, d = rd;
+      float4 cb = rcb;
+      // advance the pipeline: this step's prefetched registers are consumed below
+      cmask = nmask;
+      cid = nid;
+      {
+        const uint32_t q = ((step + 2) << 5) + lane;
+        nmask = 0u;
+        if (q < len) {
+          nmask = smask[q];
+          nid = plist[q];
+        }
       }
+      if ((cmask & umask) != 0u) {
+        const uint32_t id = min(cid, P - 1u);
+        const float4 *r = rec + 4 * (size_t)id;
+        ra = __ldg(r); rb = __ldg(r + 1); rc = __ldg(r + 2); rd = __ldg(r + 3);
+        rcb = __ldg(cull + id);
+      }
+      if (lane == 0) st.word_a[gsteps] = st.word_b[gsteps] = 0u;
+      if (vote) {
+        if (hit) {
+          const int slot = nent + __popc(vote & lt);
+          st.rec[slot][0] = a; st.rec[slot][1] = b; st.rec[slot][2] = c; st.rec[slot][3] = d;
+          // x is periodic: bring the box into the first period in which it can reach this block
+          // (the smallest shift that puts its right edge at or beyond the block's left edge),
+          // once per entry; a pixel of the block is then inside the box in that period or - a
+          // box almost a period wide - beyond the left edge of the next one.  A box without
+          // culling information (+-inf, or not meaningful at all) accepts every pixel.
+          if (!cull_on) cb = make_float4(-3.0e38f, 3.0e38f, -3.0e38f, 3.0e38f);
+          if (cb.x > -3.0e38f && cb.y < 3.0e38f) {
+            const float k = ceilf(((float)x0 - cb.y) * inv_period) * period;
+            cb.x += k;
+            cb.y += k;
+          }
+          // the quarter-pixel margin of the box (dssr_preprocess.cu:cull_box) dwarfs the
+          // rounding of the shift (< 1e-3 pixel on images up to 8192 wide)
+          st.cull[slot] = cb;
+          st.cut[slot] = rho_cutoff(d.x);
+          st.ent_pos[slot] = (step << 5) + lane + 1u;      // the reference's `contributor`
+          st.ent_mask[slot] = 0u;
+        }
+        __syncwarp();
+        const int ns = __popc(vote);
+        for (int k = 0; k < ns; k++) {
+          const int slot = nent + k;
+          const float4 cb = st.cull[slot];
+          // (written so that a NaN in the box answers "candidate")
+          const bool cand = !ps.done && !(pyf < cb.z) && !(pyf > cb.w) &&
+                            ((!(pxf < cb.x) && !(pxf > cb.y)) || !(pxf < cb.x + period));
+          const uint32_t cv = __ballot_sync(full, cand);
+          if (cand) st.queue[pending + __popc(cv & lt)] = (uint16_t)((slot << 5) | lane);
+          pending += __popc(cv);
+        }
+        nent += ns;
+      }
+      step++;
+      gsteps++;
     }
-    float4 na, nb, nc, nd;
-    if (nhit) {
-      const float4 *r = rec + 4 * (size_t)id1;
-      na = __ldg(r); nb = __ldg(r + 1); nc = __ldg(r + 2); nd = __ldg(r + 3);
-    }
-    // ---- composite this step's survivors, two at a time ----
-    const int nsurv = __popc(m);
 #ifdef RENDER_TRACE
-    n_steps++;
-    n_pairs += (nsurv + 1) / 2;
+    n_steps += gsteps;
+    n_pairs += pending;
 #endif
-    for (int pair = 0; pair < nsurv; pair += 2) {
-      // lanes 0-15 take survivor `pair`, lanes 16-31 survivor `pair + 1`
-      const int slot = pair + half;
-      const bool mine = slot < nsurv;
-      const int sl = mine ? slot : pair;
-      const SurfelRec s = unpack_rec(s_rec[cur][sl][0], s_rec[cur][sl][1], s_rec[cur][sl][2],
-                                     s_rec[cur][sl][3]);
+    __syncwarp();
+
+    // ---- evaluate and blend the queued pairs, 32 at a time ----
+    for (uint32_t base = 0; base < pending; base += 32) {
+      const uint32_t g = base + lane;
+      const bool valid = g < pending;
+      const uint32_t item = valid ? st.queue[g] : (uint32_t)lane;
+      const int slot = item >> 5, pixel = item & 31;
+      const SurfelRec s = unpack_rec(st.rec[slot][0], st.rec[slot][1], st.rec[slot][2],
+                                     st.rec[slot][3]);
+      PixelRay ray;
+      ray.X = st.ray[0][pixel];  ray.Y = st.ray[1][pixel];  ray.Z = st.ray[2][pixel];
+      ray.ax = st.ray[3][pixel]; ray.ay = st.ray[4][pixel];
+      ray.ex = st.ray[5][pixel]; ray.ey = st.ray[6][pixel]; ray.ez = st.ray[7][pixel];
+      ray.pxf = st.ray[8][pixel]; ray.pyf = st.ray[9][pixel];
       Hit h;
-      const bool maybe = mine && !ps.done && intersect_begin(ray, s, s_cut[cur][sl], h);
-      // the cull box is only a box: skip the expensive half when no pixel can pass
-      if (!__any_sync(0xffffffffu, maybe)) continue;
-      const bool ok = maybe && intersect_finish(ray, s, h);
-      // swap results between the halves: every lane gets (first, second) for its pixel
-      const bool ok_o = __shfl_xor_sync(0xffffffffu, (int)ok, 16) != 0;
-      const float alpha_o = __shfl_xor_sync(0xffffffffu, h.alpha, 16);
-      const float depth_o = __shfl_xor_sync(0xffffffffu, h.depth, 16);
-      const bool ok1 = half ? ok_o : ok, ok2 = half ? ok : ok_o;
-      bool b1 = false, b2 = false;
-      if (ok1) {
-        const float4 c = s_rec[cur][pair][2];
-        b1 = blend(ps, half ? alpha_o : h.alpha, half ? depth_o : h.depth, c.y, c.z, c.w,
-                   s_pos[cur][pair]);
+      const bool ok = valid && intersect_begin(ray, s, st.cut[slot], h) &&
+                      intersect_finish(ray, s, h);
+      st.pa[lane] = ok ? h.alpha : 0.0f;
+      st.pd[lane] = ok ? h.depth : 0.0f;
+      st.pe[lane] = (uint32_t)slot;
+      st.pmask[lane] = 0u;
+      __syncwarp();
+      if (ok) atomicOr(&st.pmask[pixel], 1u << lane);
+      __syncwarp();
+      // every pixel's own lane blends its pairs of the batch, in list order
+      {
+        uint32_t m = st.pmask[lane];
+        while (__any_sync(full, m != 0u && !ps.done)) {
+          if (m != 0u && !ps.done) {
+            const int q = __ffs(m) - 1;
+            m &= m - 1u;
+            const uint32_t e = st.pe[q];
+            const float4 c = st.rec[e][2];
+            // book-keeping for the backward: this pixel blended entry e
+            if (blend(ps, st.pa[q], st.pd[q], c.y, c.z, c.w, st.ent_pos[e])) {
+              atomicOr(&st.ent_mask[e], 1u << lane);
+              npairs++;
+            }
+          }
+        }
       }
-      if (ok2 && !ps.done) {
-        const float4 c = s_rec[cur][pair + 1][2];
-        b2 = blend(ps, half ? h.alpha : alpha_o, half ? h.depth : depth_o, c.y, c.z, c.w,
-                   s_pos[cur][pair + 1]);
-      }
-      // (both halves carry the same 16 pixel states: the low half's votes are the pixel mask)
-      const uint32_t m1 = __ballot_sync(0xffffffffu, b1) & 0xffffu;
-      const uint32_t m2 = __ballot_sync(0xffffffffu, b2) & 0xffffu;
-      if (m1) {
-        const uint32_t q = s_pos[cur][pair] - 1u;
-        if (lane == 0) pix[q] = (uint16_t)m1;
-        step_bits |= 1u << (q & 31u);
-        npairs += __popc(m1);
-      }
-      if (m2) {
-        const uint32_t q = s_pos[cur][pair + 1] - 1u;
-        if (lane == 0) pix[q] = (uint16_t)m2;
-        step_bits |= 1u << (q & 31u);
-        npairs += __popc(m2);
-      }
-      if (__all_sync(0xffffffffu, ps.done)) break;
+      __syncwarp();
+      if (__all_sync(full, ps.done)) break;
     }
-    if (lane == 0) step_word[(base - range.x) >> 5] = step_bits;
-    step_bits = 0u;
-    // ---- park the next step's records in the other buffer ----
-    if (nhit) {
-      const int slot = __popc(nm & lt);
-      s_rec[cur ^ 1][slot][0] = na; s_rec[cur ^ 1][slot][1] = nb;
-      s_rec[cur ^ 1][slot][2] = nc; s_rec[cur ^ 1][slot][3] = nd;
-      s_cut[cur ^ 1][slot] = rho_cutoff(nd.x);
-      s_pos[cur ^ 1][slot] = base - range.x + 32 + lane + 1;
+
+    // ---- write down what was blended in this phase's steps ----
+    for (int e = lane; e < nent; e += 32) {
+      const uint32_t m = st.ent_mask[e];
+      if (m) {
+        const uint32_t q = st.ent_pos[e] - 1u;
+        const uint32_t bit = 1u << (q & 31u);
+        const uint32_t k = (q >> 5) - step0;
+        if (m & 0xffffu) {
+          pix_a[q] = (uint16_t)(m & 0xffffu);
+          atomicOr(&st.word_a[k], bit);
+        }
+        if (m >> 16) {
+          pix_b[q] = (uint16_t)(m >> 16);
+          atomicOr(&st.word_b[k], bit);
+        }
+      }
     }
-    m = nm;
+    __syncwarp();
+    if (lane < gsteps) {
+      words_a[step0 + lane] = st.word_a[lane];
+      words_b[step0 + lane] = st.word_b[lane];
+    }
     __syncwarp();
   }
 
@@ -249,10 +343,11 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
     g_rtrace[work][3] = range.y - range.x;
   }
 #endif
-  // what the backward will have to do for this sub-tile: the number of blended (pixel, entry)
+  // what the backward will have to do for this block: the number of blended (pixel, entry)
   // pairs (its warps are numbered by decreasing cost, see bwd_order_kernel)
-  if (lane == 0) sub_cost[tile * SUBS_PER_TILE + sub] = npairs;
-  if (inside && half == 0) {
+  npairs = __reduce_add_sync(full, npairs);
+  if (lane == 0) unit_cost[tile * UNITS_PER_TILE + unit] = npairs;
+  if (inside) {
     const size_t HW = (size_t)W * H;
     const size_t pix = (size_t)py * W + px;
     final_T[pix] = ps.T;
@@ -270,9 +365,8 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
   }
 }
 
-// bwd_order[rank] = backward work unit (two horizontally adjacent sub-tiles = 8x4 pixels, unit
-// u = sub-tiles 2u and 2u+1), by decreasing cost = blended pairs (counting sort on cost / 32,
-// one CTA).  On large images the backward's warps run in more than one wave; longest-first
+// bwd_order[rank] = backward work unit (the forward's 8x4 pixel blocks), by decreasing cost =
+// blended pairs (counting sort on cost / 32, one CTA).  On large images the backward's warps run in more than one wave; longest-first
 // numbering packs the waves.
 // Blocks 1.. of the same launch zero the backward's accumulation buffers (`fill`: four float
 // arrays) meanwhile: one launch instead of fills and a kernel one after the other.
@@ -306,8 +400,7 @@ bwd_order_kernel(const uint32_t *__restrict__ sub_cost, int units, uint32_t *__r
   for (int b = tid; b < COST_BINS; b += 1024) s_bin[b] = 0u;
   __syncthreads();
   for (int u = tid; u < units; u += 1024)
-    atomicAdd(&s_bin[COST_BINS - 1 - min((sub_cost[2 * u] + sub_cost[2 * u + 1]) >> 5,
-                                         (uint32_t)COST_BINS - 1u)], 1u);
+    atomicAdd(&s_bin[COST_BINS - 1 - min(sub_cost[u] >> 5, (uint32_t)COST_BINS - 1u)], 1u);
   __syncthreads();
   // exclusive scan, two bins per thread
   const uint32_t v0 = s_bin[2 * tid], v1 = s_bin[2 * tid + 1];
@@ -326,8 +419,8 @@ bwd_order_kernel(const uint32_t *__restrict__ sub_cost, int units, uint32_t *__r
   s_bin[2 * tid + 1] = before + inc - v1;
   __syncthreads();
   for (int u = tid; u < units; u += 1024)
-    order[atomicAdd(&s_bin[COST_BINS - 1 - min((sub_cost[2 * u] + sub_cost[2 * u + 1]) >> 5,
-                                               (uint32_t)COST_BINS - 1u)], 1u)] = (uint32_t)u;
+    order[atomicAdd(&s_bin[COST_BINS - 1 - min(sub_cost[u] >> 5, (uint32_t)COST_BINS - 1u)], 1u)] =
+        (uint32_t)u;
 }
 
 }  // namespace
@@ -344,8 +437,8 @@ void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageVie
   if (first_use_on_device(seen))   // one-warp CTAs: residency is limited by the carve-out
     cudaFuncSetAttribute(render_forward_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                          cudaSharedmemCarveoutMaxShared);
-  render_forward_kernel<<<im.tiles * SUBS_PER_TILE, 32, 0, LS(s)>>>(
-      im.ranges, order, b.point_list, b.sub_mask, g.rec, p.projmatrix, p.W, p.H, im.tiles_x,
+  render_forward_kernel<<<im.tiles * UNITS_PER_TILE, 32, 0, LS(s)>>>(
+      im.ranges, order, b.point_list, b.sub_mask, g.rec, g.cull, p.projmatrix, p.W, p.H, im.tiles_x,
       capacity, (uint32_t)p.P, im.final_T, im.n_contrib, p.out_maps, im.sub_cost, b.blend_bits,
       b.bits_stride, b.pix_mask, b.pix_stride);
 }

@@ -120,6 +120,40 @@ __device__ __forceinline__ bool intersect_finish(const PixelRay &r, const Surfel
   return true;
 }
 
+// Both halves without a branch, for callers that know the pair passes (the backward composites
+// exactly the pairs the forward blended): the same operations on the same values in the same
+// order - only the early exits are gone - so every field equals what intersect_begin +
+// intersect_finish leave behind.  Returns what they would have returned.
+__device__ __forceinline__ bool intersect_all(const PixelRay &r, const SurfelRec &s, Hit &h) {
+  h.kx = FF(0.0f, s.tuz, FF(s.tux, r.ax, FM(s.tuy, r.ay)));
+  h.ky = FF(0.0f, s.tvz, FF(s.tvx, r.ax, FM(s.tvy, r.ay)));
+  h.kz = FF(0.0f, s.twz, FF(s.twx, r.ax, FM(s.twy, r.ay)));
+  h.lx = FF(s.tuz, r.ez, FF(s.tux, r.ex, FM(s.tuy, r.ey)));
+  h.ly = FF(s.tvz, r.ez, FF(s.tvx, r.ex, FM(s.tvy, r.ey)));
+  h.lz = FF(s.twz, r.ez, FF(s.twx, r.ex, FM(s.twy, r.ey)));
+  h.pz = FF(h.kx, h.ly, -FM(h.ky, h.lx));
+  h.px = FF(h.ky, h.lz, -FM(h.kz, h.ly));
+  h.py = FF(h.kz, h.lx, -FM(h.kx, h.lz));
+  h.dx = FS(s.cx, r.pxf);
+  h.dy = FS(s.cy, r.pyf);
+  const float t = FF(h.dy, h.dy, FM(h.dx, h.dx));
+  h.rho2d = FA(t, t);
+  h.sx = __fdiv_rn(h.px, h.pz);
+  h.sy = __fdiv_rn(h.py, h.pz);
+  h.rho3d = FF(h.sx, h.sx, FM(h.sy, h.sy));
+  h.bx = FA(s.twx, FF(s.tux, h.sx, FM(s.tvx, h.sy)));
+  h.by = FA(s.twy, FF(s.tuy, h.sx, FM(s.tvy, h.sy)));
+  h.bz = FA(s.twz, FF(s.tuz, h.sx, FM(s.tvz, h.sy)));
+  const float valid = FF(r.Z, h.bz, FF(r.X, h.bx, FM(r.Y, h.by)));
+  const float d3 = __fsqrt_rn(FF(h.bz, h.bz, FF(h.bx, h.bx, FM(h.by, h.by))));
+  h.depth = (h.rho3d <= h.rho2d) ? d3 : s.d2d;
+  const float power = FM(fminf(h.rho3d, h.rho2d), -0.5f);
+  h.G = expf(power);
+  h.alpha = fminf(0.99f, FM(s.opa, h.G));
+  return !(h.pz == 0.0f) && !(valid < 0.0f) && !(h.depth < SPLAT_NEAR) && !(power > 0.0f) &&
+         !(h.alpha < __uint_as_float(SPLAT_ALPHA_MIN));
+}
+
 // Does the surfel's cull box (see dssr_preprocess.cu:cull_box) touch the pixel
 // rectangle [x0,x1] x [y0,y1]?  x is periodic with the azimuth period.  Written so
 // that any NaN answers "yes".

@@ -102,6 +102,16 @@ class SplatAdamArgs(ctypes.Structure):
     ]
 
 
+class GsaPhotoParams(ctypes.Structure):
+    _fields_ = [
+        ("H", ctypes.c_int), ("W", ctypes.c_int),
+        ("fx", ctypes.c_float), ("fy", ctypes.c_float), ("cx", ctypes.c_float), ("cy", ctypes.c_float),
+        ("min_depth", ctypes.c_float), ("max_depth", ctypes.c_float),
+        ("omega_depth", ctypes.c_float), ("depth_rejection_threshold", ctypes.c_float),
+        ("kernel_chi_threshold", ctypes.c_float), ("stream", ctypes.c_void_p),
+    ]
+
+
 POST_LOSS_WORKSPACE_BYTES = 64
 
 # every symbol include/splat_b200.h declares
@@ -116,6 +126,8 @@ EXPORTS = (
     "dssr_post_loss_forward", "dssr_post_loss_backward", "splat_activation_adam_step",
     "splat_xchg_fault", "splat_launch_count", "splat_compact_workspace_bytes",
     "splat_compact_plan", "splat_compact_rows", "splat_append_rows",
+    "gsa_photo_workspace_bytes", "gsa_photo_set_reference", "gsa_photo_set_query",
+    "gsa_photo_align", "gsa_photo_debug_reference",
 )
 XCHG_HANDLE_BYTES = 64
 SURGERY_MAX_TENSORS = 12
@@ -203,6 +215,19 @@ def load():
     lib.splat_compact_rows.restype = ctypes.c_int
     lib.splat_append_rows.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, pp, pp, pp, ip, vp]
     lib.splat_append_rows.restype = ctypes.c_int
+    fl = ctypes.c_float
+    lib.gsa_photo_workspace_bytes.argtypes = [ctypes.c_int, ctypes.c_int]
+    lib.gsa_photo_workspace_bytes.restype = ctypes.c_size_t
+    lib.gsa_photo_set_reference.argtypes = [vp, ctypes.c_int, ctypes.c_int, vp, fl, ctypes.c_int, vp]
+    lib.gsa_photo_set_reference.restype = ctypes.c_int
+    lib.gsa_photo_set_query.argtypes = [vp, ctypes.c_int, ctypes.c_int, vp, fl, fl, fl, fl, fl, fl, vp]
+    lib.gsa_photo_set_query.restype = ctypes.c_int
+    lib.gsa_photo_debug_reference.argtypes = [vp, ctypes.c_int, ctypes.c_int, vp, vp]
+    lib.gsa_photo_debug_reference.restype = ctypes.c_int
+    lib.gsa_photo_align.argtypes = [vp, ctypes.POINTER(GsaPhotoParams), ctypes.POINTER(fl),
+                                    ctypes.c_int, ctypes.POINTER(fl), ctypes.POINTER(fl),
+                                    ctypes.POINTER(ctypes.c_double)]
+    lib.gsa_photo_align.restype = ctypes.c_int
     lib.splat_launch_count.argtypes = []
     lib.splat_launch_count.restype = ctypes.c_ulonglong
     for f in (lib.splat_xchg_create, lib.splat_xchg_export, lib.splat_xchg_connect,

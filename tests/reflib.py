@@ -164,3 +164,71 @@ def dist2(points, sync=True):
     if rc != 0:
         raise RuntimeError("reference distCUDA2 failed")
     return out
+
+
+# ---- the reference's photometric registration (oracle/_ref/libref_photo.so) ----------------
+REF_PHOTO_LIB = os.path.join(_ROOT, "oracle", "_ref", "libref_photo.so")
+_photo = None
+
+
+def photo_available():
+    return os.path.exists(REF_PHOTO_LIB) and torch.cuda.is_available()
+
+
+class RefPhotometric:
+    """PhotometricFac + ImageSet of the reference's gsaligner submodule, configured as
+    GSAligner configures them (oracle/ref_photo_shim.cu)."""
+
+    def __init__(self, H, W, omega_depth=5.0, depth_rejection_threshold=0.8, rho_kernel=1.0,
+                 min_depth=0.5, max_depth=80.0):
+        global _photo
+        if _photo is None:
+            lib = ctypes.CDLL(REF_PHOTO_LIB)
+            vp, fl = ctypes.c_void_p, ctypes.c_float
+            lib.ref_photo_create.restype = vp
+            lib.ref_photo_create.argtypes = [ctypes.c_int, ctypes.c_int, fl, fl, fl, fl, fl]
+            lib.ref_photo_destroy.argtypes = [vp]
+            lib.ref_photo_set_reference.argtypes = [vp, vp, ctypes.POINTER(fl)]
+            lib.ref_photo_set_query.argtypes = [vp, vp]
+            lib.ref_photo_align.argtypes = [vp, ctypes.POINTER(fl), ctypes.c_int,
+                                            ctypes.POINTER(fl), ctypes.POINTER(fl)]
+            lib.ref_photo_linearize.argtypes = [vp, ctypes.POINTER(fl), ctypes.POINTER(ctypes.c_double)]
+            lib.ref_photo_reference_image.argtypes = [vp, ctypes.POINTER(fl)]
+            _photo = lib
+        self.lib, self.H, self.W = _photo, H, W
+        self.h = self.lib.ref_photo_create(H, W, omega_depth, depth_rejection_threshold,
+                                           rho_kernel, min_depth, max_depth)
+
+    def __del__(self):
+        try:
+            self.lib.ref_photo_destroy(self.h)
+        except Exception:
+            pass
+
+    def set_reference(self, depth, K):
+        torch.cuda.synchronize()
+        self._ref = depth.contiguous().float()
+        k = (ctypes.c_float * 9)(*[float(x) for x in K.reshape(-1)])
+        assert self.lib.ref_photo_set_reference(self.h, self._ref.data_ptr(), k) == 0
+
+    def set_query(self, depth):
+        torch.cuda.synchronize()
+        self._query = depth.contiguous().float()
+        assert self.lib.ref_photo_set_query(self.h, self._query.data_ptr()) == 0
+
+    def align(self, T, iterations):
+        t = (ctypes.c_float * 16)(*[float(x) for x in T.reshape(-1)])
+        out, stats = (ctypes.c_float * 16)(), (ctypes.c_float * 2)()
+        assert self.lib.ref_photo_align(self.h, t, iterations, out, stats) == 0
+        return torch.tensor(list(out)).reshape(4, 4), float(stats[1]), float(stats[0])
+
+    def linearize(self, T):
+        t = (ctypes.c_float * 16)(*[float(x) for x in T.reshape(-1)])
+        out = (ctypes.c_double * 30)()
+        assert self.lib.ref_photo_linearize(self.h, t, out) == 0
+        return list(out)
+
+    def reference_image(self):
+        out = (ctypes.c_float * (4 * self.H * self.W))()
+        assert self.lib.ref_photo_reference_image(self.h, out) == 0
+        return torch.tensor(list(out)).reshape(4, self.H, self.W)

@@ -242,3 +242,38 @@ def input_digest(s):
     for k in ("means3D", "scales", "rotations", "opacities", "viewmatrix", "projmatrix", "dL_dout"):
         h.update(np.ascontiguousarray(s[k]).tobytes())
     return h.hexdigest()
+
+
+def room_range_image(H, W, vfov_deg, pose=None, half=(9.0, 6.0, 2.5), holes=0.02, seed=0):
+    """Range image of the inside of a box room (plus a pillar) seen by a spherical sensor at
+    `pose` (4x4 world_T_sensor), with K as in `intrinsics`; `holes`: fraction of pixels without a
+    return (0).  For the photometric-registration tests."""
+    K = intrinsics(H, W, vfov_deg)[:3, :3].T.astype(np.float64)
+    pose = np.eye(4) if pose is None else np.asarray(pose, dtype=np.float64)
+    col, row = np.meshgrid(np.arange(W, dtype=np.float64), np.arange(H, dtype=np.float64))
+    az, el = (col - K[0, 2]) / K[0, 0], (row - K[1, 2]) / K[1, 1]
+    d = np.stack([np.cos(az) * np.cos(el), np.sin(az) * np.cos(el), np.sin(el)], -1) @ pose[:3, :3].T
+    o = pose[:3, 3]
+    t = np.full((H, W), np.inf)
+    for ax in range(3):
+        for sgn in (-1.0, 1.0):
+            with np.errstate(divide="ignore", invalid="ignore"):
+                tt = (sgn * half[ax] - o[ax]) / d[..., ax]
+            tt[~(tt > 0)] = np.inf
+            t = np.minimum(t, tt)
+    # a vertical pillar of radius 0.7 at (4, 2)
+    cxy, rad = np.array([4.0, 2.0]), 0.7
+    oc = o[:2] - cxy
+    a = d[..., 0] ** 2 + d[..., 1] ** 2
+    b = 2 * (d[..., 0] * oc[0] + d[..., 1] * oc[1])
+    c = oc @ oc - rad * rad
+    disc = b * b - 4 * a * c
+    with np.errstate(divide="ignore", invalid="ignore"):
+        tp = (-b - np.sqrt(np.where(disc > 0, disc, np.nan))) / (2 * a)
+    tp[~(tp > 0)] = np.inf
+    t = np.minimum(t, tp)
+    rng = np.random.default_rng(seed)
+    t = t * (1 + 0.002 * rng.standard_normal(t.shape))
+    t[rng.random(t.shape) < holes] = 0.0
+    t[~np.isfinite(t)] = 0.0
+    return t.astype(np.float32), K.astype(np.float32)

@@ -1,0 +1,42 @@
+"""CPU: the numpy restatement of the photometric registration (oracle/photometric.py) against
+golden outputs of the reference build (tests/golden/photo_*.npz, made on a GPU by
+tests/golden/make_golden_photo.py), and against the known motion of a synthetic scene."""
+import os
+
+import numpy as np
+import pytest
+
+import scenes
+from conftest import GOLDEN
+from oracle import photometric as ph
+
+
+@pytest.mark.parametrize("name", ["ref", "room"])
+def test_oracle_reproduces_the_reference(name):
+    path = os.path.join(GOLDEN, f"photo_{name}.npz")
+    g = np.load(path) if os.path.exists(path) else None
+    if g is None or "sums0" not in g.files:
+        pytest.skip("golden outputs not generated yet")
+    ref = ph.prepare_reference(g["ref"])
+    img = g["ref_image"]
+    assert np.array_equal(ref[3], img[3] > 0)
+    assert np.array_equal(ref[1], img[1]) and np.array_equal(ref[2], img[2])
+    sums = ph.linearize(ref, ph.query_cloud(g["query"], g["K"], 0.5, 80.0), g["T0"], g["K"], 0.5,
+                        80.0, 5.0, 0.8, 1.0)
+    want = g["sums0"]
+    assert np.abs(sums[:21] - want[:21]).max() <= 1e-3 * np.abs(want[:21]).max()
+    assert np.abs(sums[21:27] - want[21:27]).max() <= 1e-3 * np.abs(want[21:27]).max()
+    assert abs(sums[27] - want[27]) <= 1e-3 * want[27]
+    assert abs(sums[28] - want[28]) <= 2e-3 * want[28] + 2
+    T, stats, _ = ph.align(g["ref"], g["query"], g["K"], g["T0"], 10)
+    assert np.abs(T - g["T10"]).max() < 5e-4
+    assert abs(stats[0] - g["stats10"][0]) <= 3e-3 * g["stats10"][0] + 1e-6
+
+
+def test_oracle_recovers_a_known_motion():
+    pose = scenes.pose(1)
+    pose[:3, 3] *= 0.3
+    a, K = scenes.room_range_image(32, 256, 40.0)
+    b, _ = scenes.room_range_image(32, 256, 40.0, pose=pose, seed=1)
+    T, stats, sums = ph.align(a, b, K, np.eye(4, dtype=np.float32), 10)
+    assert np.abs(T - pose).max() < 5e-3 and sums[28] > 0.5 * a.size
