@@ -17,7 +17,6 @@ SOURCES = [
     "dssr_preprocess.cu",
     "radix_sort.cu",
     "dssr_render_fwd.cu",
-    "dssr_render_fwd_steps.cu",
     "dssr_render_bwd.cu",
     "sknn.cu",
     "peer_exchange.cu",

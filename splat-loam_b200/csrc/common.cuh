@@ -342,10 +342,6 @@ struct FillList {           // float arrays to clear (any 4-byte alignment, any 
 void launch_bwd_order(const ImageView &im, const FillList &fill, cudaStream_t s);
 void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageView &im,
                            const BinView &b, uint32_t capacity, cudaStream_t s);
-// the step-synchronous variant (one warp per 4x4 sub-tile, two entries at a time), selected
-// with SPLAT_B200_FWD=steps: kept for A/B measurements
-void launch_render_forward_steps(const FwdParams &p, const GeomView &g, const ImageView &im,
-                                 const BinView &b, uint32_t capacity, cudaStream_t s);
 
 struct BwdParams {
   int P, W, H;

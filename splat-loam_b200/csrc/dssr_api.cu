@@ -157,9 +157,7 @@ int run_binning_and_render(const dssr_forward_args *a, const FwdParams &fp,
   LAUNCH_CHECK(dbg, st, "sort");
   {
     ProfScope ps("render_forward", st);
-    static const bool steps = getenv("SPLAT_B200_FWD") && !strcmp(getenv("SPLAT_B200_FWD"), "steps");
-    if (steps) launch_render_forward_steps(fp, gv, iv, bv, capacity, st);
-    else launch_render_forward(fp, gv, iv, bv, capacity, st);
+    launch_render_forward(fp, gv, iv, bv, capacity, st);
   }
   LAUNCH_CHECK(dbg, st, "render_forward");
   return 0;

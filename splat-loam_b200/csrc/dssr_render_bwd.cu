@@ -109,10 +109,12 @@ struct __align__(16) WarpStage {
   uint32_t pmask[32];               // per pixel: which lanes of the batch hold its pairs
   float vbuf[32][13];               // P3: the pairs' 13 contributions, summed per entry
   uint16_t queue[QUEUE_CAP];        // the gathered pairs, (slot << 5) | pixel, back to front
+  float *dst_base[13];              // where component c of surfel 0 accumulates ...
+  uint32_t dst_stride[13];          // ... and the stride to the next surfel
 };
 
 // One WARP per CTA = one 8x4 pixel block; CTAs in order of decreasing number of pairs.
-__global__ void __launch_bounds__(32)
+__global__ void __launch_bounds__(32, 14)
 render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restrict__ bwd_order,
                        const uint32_t *__restrict__ point_list, const char *__restrict__ bin_base,
                        const BinHeader *__restrict__ bhdr, const float4 *__restrict__ rec,
@@ -194,14 +196,19 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
     pc.gReg = dL_dout[pix + 6 * HW];
   }
   st.gN[0][lane] = pc.gN0; st.gN[1][lane] = pc.gN1; st.gN[2][lane] = pc.gN2;
+  if (lane < 13) {   // components 0-8: dL_dtransMat rows (stride 12, 4 per row), 9-11: normal, 12: opacity
+    st.dst_base[lane] = lane < 9 ? dL_dtransMat + (lane / 3) * 4 + (lane % 3)
+                                 : (lane < 12 ? dL_dnormal + (lane - 9) : dL_dopacity);
+    st.dst_stride[lane] = lane < 9 ? 12u : (lane < 12 ? 3u : 1u);
+  }
 
   const int top_a = max_a ? (int)((max_a - 1) >> 5) : -1, top_b = max_b ? (int)((max_b - 1) >> 5) : -1;
   int chunk = (int)((max_last - 1) >> 5);
   const uint32_t lt = (1u << lane) - 1u;
-  // Software pipeline of the walk (back to front): the step words are fetched three steps
-  // ahead of their use, the blended entries' surfel indices and pixel masks two steps ahead,
-  // their records one step ahead (into registers) - each load's L2 latency sits under the
-  // work on the steps before it.
+  // Software pipeline of the walk (back to front): the step words are fetched four steps
+  // ahead of their use, the blended entries' surfel indices and pixel masks three steps ahead,
+  // their records one step ahead (into registers) - every load's address comes from a load
+  // issued at least two steps earlier, so its L2 latency sits under the work in between.
   auto load_words = [&](int c, uint32_t &wa, uint32_t &wb) {
     wa = (c >= 0 && c <= top_a) ? words_a[c] : 0u;
     wb = (c >= 0 && c <= top_b) ? words_b[c] : 0u;
@@ -216,16 +223,18 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
       if ((wb >> lane) & 1u) mask |= (uint32_t)pm_b[q] << 16;
     }
   };
-  uint32_t w0a, w0b, w1a, w1b, w2a, w2b;           // words of chunk, chunk - 1, chunk - 2
+  uint32_t w0a, w0b, w1a, w1b, w2a, w2b, w3a, w3b;  // words of chunk .. chunk - 3
   load_words(chunk, w0a, w0b);
   load_words(chunk - 1, w1a, w1b);
   load_words(chunk - 2, w2a, w2b);
-  uint32_t id0, mask0, id1, mask1;                  // entries of chunk, chunk - 1
+  load_words(chunk - 3, w3a, w3b);
+  uint32_t id0, mask0, id1, mask1, id2, mask2;      // entries of chunk .. chunk - 2
   load_entry(chunk, w0a, w0b, id0, mask0);
   load_entry(chunk - 1, w1a, w1b, id1, mask1);
+  load_entry(chunk - 2, w2a, w2b, id2, mask2);
   float4 ra, rb, rc, rd;                            // records of chunk
   ra = rb = rc = rd = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (mask0) {
+  if (((w0a | w0b) >> lane) & 1u) {
     const float4 *r = rec + 4 * (size_t)id0;
     ra = __ldg(r); rb = __ldg(r + 1); rc = __ldg(r + 2); rd = __ldg(r + 3);
   }
@@ -240,11 +249,11 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
       const uint32_t id = id0, mask = mask0;
       const float4 a = ra, b = rb, c = rc, d = rd;
       // advance the pipeline
-      w0a = w1a; w0b = w1b; w1a = w2a; w1b = w2b;
-      load_words(chunk - 3, w2a, w2b);
-      id0 = id1; mask0 = mask1;
-      load_entry(chunk - 2, w1a, w1b, id1, mask1);
-      if (mask0) {
+      w0a = w1a; w0b = w1b; w1a = w2a; w1b = w2b; w2a = w3a; w2b = w3b;
+      load_words(chunk - 4, w3a, w3b);
+      id0 = id1; mask0 = mask1; id1 = id2; mask1 = mask2;
+      load_entry(chunk - 3, w2a, w2b, id2, mask2);
+      if (((w0a | w0b) >> lane) & 1u) {
         const float4 *r = rec + 4 * (size_t)id0;
         ra = __ldg(r); rb = __ldg(r + 1); rc = __ldg(r + 2); rd = __ldg(r + 3);
       }
@@ -393,12 +402,7 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
           if (q < q1) s0 += st.vbuf[q][comp];
           const float sum = s0 + s1;
           if (sum != 0.0f) {
-            const size_t gid = st.ent_id[e];
-            float *dst;
-            if (comp < 9) dst = dL_dtransMat + gid * 12 + (comp / 3) * 4 + (comp % 3);
-            else if (comp < 12) dst = dL_dnormal + gid * 3 + (comp - 9);
-            else dst = dL_dopacity + gid;
-            atomicAdd(dst, sum);
+            atomicAdd(st.dst_base[comp] + (size_t)st.ent_id[e] * st.dst_stride[comp], sum);
           }
         }
       }

@@ -169,10 +169,11 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
 
   const uint32_t nsteps = (len + 31) >> 5;
   uint32_t step = 0;
-  // Software pipeline of the walk: masks and surfel indices are fetched two steps ahead of
-  // their use, the records and cull boxes of a step's entries one step ahead (into registers),
-  // so that their L2 latency sits under the previous step's tests and the evaluation phase.
-  uint32_t cmask = 0u, cid = 0u, nmask = 0u, nid = 0u;
+  // Software pipeline of the walk: masks and surfel indices are fetched three steps ahead of
+  // their use, the records and cull boxes of a step's entries one step ahead (into registers):
+  // a record's address comes from an index loaded two steps earlier, so every L2 latency sits
+  // under the tests of the steps in between and under the evaluation phase.
+  uint32_t cmask = 0u, cid = 0u, nmask = 0u, nid = 0u, n2mask = 0u, n2id = 0u;
   if (lane < len) {
     cmask = smask[lane];
     cid = plist[lane];
@@ -180,6 +181,10 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
   if (32 + lane < len) {
     nmask = smask[32 + lane];
     nid = plist[32 + lane];
+  }
+  if (64 + lane < len) {
+    n2mask = smask[64 + lane];
+    n2id = plist[64 + lane];
   }
   float4 ra, rb, rc, rd, rcb;
   ra = rb = rc = rd = rcb = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -206,12 +211,14 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
       // advance the pipeline: this step's prefetched registers are consumed below
       cmask = nmask;
       cid = nid;
+      nmask = n2mask;
+      nid = n2id;
       {
-        const uint32_t q = ((step + 2) << 5) + lane;
-        nmask = 0u;
+        const uint32_t q = ((step + 3) << 5) + lane;
+        n2mask = 0u;
         if (q < len) {
-          nmask = smask[q];
-          nid = plist[q];
+          n2mask = smask[q];
+          n2id = plist[q];
         }
       }
       if ((cmask & umask) != 0u) {

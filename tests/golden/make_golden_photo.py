@@ -8,7 +8,14 @@ Cases: the reference's own fixture (submodules/gsaligner/tests/data/depth_{ref,q
 K_ref.npy - read from /root/reference when present, else from an earlier photo_ref.npz) and a
 small synthetic room.  Stored per case: both range images, K, the initial guess, the prepared
 reference image (depth, derivatives, mask), the 30 sums of the first linearisation, and the
-transform + stats after 1 and 10 iterations."""
+transform + stats after 1 and 10 iterations.
+
+The initial guess is a small GENERIC motion, not the identity: at the identity every query
+point re-projects onto (numerically almost exactly) an integer pixel, so the truncation in
+getSubPixel and the +-0.5 rounding of the z-buffer pixel are decided by the last bit of the
+sin / cos / atan2 chain - the sums then move by several per cent under a 1e-5 pixel nudge and
+are no basis for a comparison.  The transform after 10 iterations FROM the identity (what the
+reference's own test does) is stored as well; it is compared with a looser tolerance."""
 import os
 import sys
 
@@ -34,6 +41,8 @@ def run(name, ref, query, K, T0, out):
         T, fit, err = r.align(T0, it)
         res[f"T{it}"] = T.numpy()
         res[f"stats{it}"] = np.array([err, fit], dtype=np.float32)     # residual, inlier ratio
+    T, fit, err = r.align(np.eye(4, dtype=np.float32), 10)
+    res["T10_identity"] = T.numpy()
     np.savez_compressed(os.path.join(out, f"photo_{name}.npz"), **res)
     print(name, res["sums0"][27:], res["stats10"], "\n", res["T10"])
 
@@ -48,12 +57,12 @@ def main():
         g = np.load(os.path.join(HERE, "photo_ref.npz"))
         ref, query, K = g["ref"], g["query"], g["K"]
     run("ref", ref.astype(np.float32), query.astype(np.float32), K.astype(np.float32),
-        np.eye(4, dtype=np.float32), out)
+        scenes.small_motion(), out)
     pose = scenes.pose(1)
     pose[:3, 3] *= 0.3
     a, K = scenes.room_range_image(32, 256, 40.0)
     b, _ = scenes.room_range_image(32, 256, 40.0, pose=pose, seed=1)
-    run("room", a, b, K, np.eye(4, dtype=np.float32), out)
+    run("room", a, b, K, scenes.small_motion(), out)
 
 
 if __name__ == "__main__":

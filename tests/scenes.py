@@ -277,3 +277,16 @@ def room_range_image(H, W, vfov_deg, pose=None, half=(9.0, 6.0, 2.5), holes=0.02
     t[rng.random(t.shape) < holes] = 0.0
     t[~np.isfinite(t)] = 0.0
     return t.astype(np.float32), K.astype(np.float32)
+
+
+def small_motion():
+    """A generic small rigid motion (13 mm, -21 mm, 4 mm; 0.17 / -0.11 / 0.23 degrees): the
+    initial guess of the photometric-registration comparisons (see make_golden_photo.py)."""
+    rx, ry, rz = 0.003, -0.002, 0.004
+    Rx = np.array([[1, 0, 0], [0, math.cos(rx), -math.sin(rx)], [0, math.sin(rx), math.cos(rx)]])
+    Ry = np.array([[math.cos(ry), 0, math.sin(ry)], [0, 1, 0], [-math.sin(ry), 0, math.cos(ry)]])
+    Rz = np.array([[math.cos(rz), -math.sin(rz), 0], [math.sin(rz), math.cos(rz), 0], [0, 0, 1]])
+    T = np.eye(4)
+    T[:3, :3] = Rz @ Ry @ Rx
+    T[:3, 3] = [0.013, -0.021, 0.004]
+    return T.astype(np.float32)

