@@ -6,14 +6,14 @@
 A "step" is one pass of the hot path over one synthetic frame per GPU: rasterizer forward +
 backward through the reference-facing `_C` calls (which go through the C-ABI of
 libsplat_b200.so).  N=1 runs BASELINE config C2 (64x1024 image, 500k surfels).  N>1 is the
-keyframe-sharded window (weak scaling): rank r renders keyframe r (BASELINE poses: 0.5 m and
-2 degrees of yaw per keyframe) of the same surfel set and the per-surfel [P,10] gradient
-buffers are summed over NVLink peer memory (push fused into the VJP kernel;
+keyframe-sharded window (weak scaling): rank r renders its own keyframe of the same surfel set
+(equal work per GPU, see scene_tensors) and the per-surfel [P,10] gradient buffers are summed
+over NVLink peer memory (push fused into the VJP kernel;
 SPLAT_B200_XCHG=nccl selects one NCCL all-reduce instead); before anything is timed the
 exchange's sum is checked against an NCCL all-reduce of the same buffers
 (`exchange_check`).  At N>1 the line also carries `window`: the BASELINE window configs
-(C3: 8 keyframes at 2/4/8 GPUs, C4: 32 keyframes at 8) through KeyframeWindow.gradients,
-with the same window timed on ONE GPU in the same run.
+(C3: 8 keyframes at 2/4/8 GPUs, C4: 32 keyframes at 8, BASELINE.md's poses) through
+KeyframeWindow.gradients, with the same window timed on ONE GPU in the same run.
 
 Rank 0 prints ONE JSON line.  See DESIGN.md "Measurement" for every field.
 """
@@ -127,9 +127,15 @@ class ClockSampler:
 
 
 def scene_tensors(cfg, keyframe, device, pinned=False):
-    # keyframe k of the window: BASELINE.md section 3's poses (0.5 m * k along x, 2 deg * k of
-    # yaw) over ONE surfel set (seed 0) - the frames of a window do not cost exactly the same
-    s = scenes.make_scene(cfg, keyframe=keyframe)
+    # The weak-scaling line measures what the exchange costs on top of a frame, so every GPU
+    # gets the SAME work: rank r's keyframe is the scene rotated by 22.5 degrees * r about the
+    # sensor's vertical axis (ranges and footprints unchanged).  BASELINE.md's poses (0.5 m and
+    # 2 degrees per keyframe) move the sensor through the synthetic cloud and change a frame's
+    # cost by up to 40 % (its longest tile list: 5.3k entries at keyframe 0, 7.4k at keyframe 1,
+    # CPU oracle) - a step would then time the slowest keyframe, not the exchange.  Those poses
+    # are what the `window` entries run (run_window), where the keyframes are dealt round-robin.
+    s = scenes.make_scene(cfg, keyframe=0)
+    s["viewmatrix"] = scenes.yaw_viewmatrix(22.5 * keyframe)
     t = {}
     for k in ("means3D", "opacities", "scales", "rotations", "viewmatrix", "projmatrix", "dL_dout"):
         x = torch.from_numpy(s[k])
@@ -141,7 +147,7 @@ def scene_tensors(cfg, keyframe, device, pinned=False):
 def workload(cfg, H, W, P):
     """The same string for both arms (the implementation goes under config.implementation)."""
     return (f"{cfg}: {H}x{W} spherical range image, {P} surfels, fwd+bwd per frame, one keyframe "
-            "per GPU (keyframe r on rank r)")
+            "per GPU (rank r: the scene yawed by 22.5 deg * r - equal work on every GPU)")
 
 
 L2_NOTE = "192 MB buffer (1.5x the 126 MB L2) written between timed steps"
