@@ -494,6 +494,7 @@ def run_ours(args, rank, world, local_rank):
     if world == 1:
         line["post"] = post_stage(allmap.detach(), t)
         line["optimizer"] = adam_stage(P, dev)
+        line["photometric"] = photometric_stage(dev)
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args.config)
     return line
@@ -548,6 +549,48 @@ def run_window(cfg, K, rank, world, dev, flush, reps=10):
             "keyframes": K, "ms_per_window": t_g, "keyframes_per_s": K * 1e3 / t_g,
             "ms_per_window_1gpu": t_1, "of_linear": t_1 / (world * t_g),
             "rel_err_vs_1gpu": float(rel[0])}
+
+
+def photometric_stage(dev, iters=20):
+    """SURVEY.md §8(f) rank 3, reported beside the headline: one photometric alignment (10
+    Gauss-Newton iterations, 64x1024 range images of a synthetic room, generic initial guess)
+    through gsaligner_photometric.PhotometricAligner, and through the unmodified reference
+    build (oracle/_ref/libref_photo.so) when it is there.  Wall-clock per call: both end with
+    the transform on the host."""
+    from gsaligner_photometric import PhotometricAligner
+    import reflib
+    a, K = scenes.room_range_image(64, 1024, 33.2, seed=2)
+    pose = scenes.pose(2)
+    pose[:3, 3] *= 0.2
+    b, _ = scenes.room_range_image(64, 1024, 33.2, pose=pose, seed=3)
+    T0 = torch.from_numpy(scenes.small_motion())
+    proj = torch.eye(4)
+    proj[:3, :3] = torch.from_numpy(K).T
+    da, db = torch.from_numpy(a)[None].to(dev), torch.from_numpy(b)[None].to(dev)
+    al = PhotometricAligner(image_height=64, image_width=1024)
+    al.set_reference(da, None, proj.to(dev))
+    al.set_query(db, None, proj.to(dev))
+
+    def clock(fn):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(iters):
+            fn()
+        torch.cuda.synchronize()
+        return (time.perf_counter() - t0) / iters * 1e3
+
+    res = {"fused_ms": clock(lambda: al.align_photometric(T0)),
+           "what": "photometric alignment, 64x1024, 10 iterations, transform back on the host"}
+    if reflib.photo_available():
+        r = reflib.RefPhotometric(64, 1024)
+        r.set_reference(da[0], K)
+        r.set_query(db[0])
+        res["reference_ms"] = clock(lambda: r.align(T0.numpy(), 10))
+        res["max_abs_diff_of_transforms"] = float(
+            (al.align_photometric(T0)[0] - r.align(T0.numpy(), 10)[0]).abs().max())
+    return res
 
 
 def adam_stage(P, dev, iters=50):
