@@ -374,16 +374,22 @@ def run_ours(args, rank, world, local_rank):
         d["viewmatrix"], d["projmatrix"] = t["viewmatrix"], t["projmatrix"]
         d_in.append(d)
     if shard:
+        # the rank's rows of the four parameter tensors travel as ONE packed [P/N,10] block:
+        # one H2D copy, one all-gather, then four strided device copies into the tensors the
+        # rasterizer reads (a collective call costs the host far more than a copy kernel)
         per = P // world
-        h_slice = {k: hp[k][rank * per:(rank + 1) * per].clone().pin_memory() for k in PARAM_KEYS}
-        d_slice = [{k: torch.empty_like(h_slice[k], device=dev) for k in PARAM_KEYS} for _ in range(2)]
+        cols = {"means3D": (0, 3), "opacities": (3, 4), "scales": (4, 6), "rotations": (6, 10)}
+        h_slice = torch.cat([hp[k][rank * per:(rank + 1) * per] for k in PARAM_KEYS], dim=1).pin_memory()
+        d_slice = [torch.empty_like(h_slice, device=dev) for _ in range(2)]
+        d_full = [torch.empty((P, 10), dtype=torch.float32, device=dev) for _ in range(2)]
 
     def copy_in(b):
         d_in[b]["dL_dout"].copy_(hp["dL_dout"], non_blocking=True)
         if shard:
-            for k in PARAM_KEYS:
-                d_slice[b][k].copy_(h_slice[k], non_blocking=True)
-                dist.all_gather_into_tensor(d_in[b][k], d_slice[b][k])
+            d_slice[b].copy_(h_slice, non_blocking=True)
+            dist.all_gather_into_tensor(d_full[b], d_slice[b])
+            for k, (c0, c1) in cols.items():
+                d_in[b][k].copy_(d_full[b][:, c0:c1])
         else:
             for k in PARAM_KEYS:
                 d_in[b][k].copy_(hp[k], non_blocking=True)
@@ -847,6 +853,7 @@ def main():
     if world > 1 and torch.cuda.is_available():
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # keep stdout to the JSON line
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", rank=rank, world_size=world,
                                 device_id=torch.device("cuda", local_rank))

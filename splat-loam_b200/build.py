@@ -53,7 +53,9 @@ def build(force=False, verbose=False):
     for src in SOURCES:
         obj = os.path.join(LIBDIR, src.replace(".cu", ".o"))
         objs.append(obj)
-        cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        # SPLAT_B200_EXTRA_NVCC_FLAGS: developer builds (-DRENDER_TRACE, -DSORT_TRACE)
+        extra = os.environ.get("SPLAT_B200_EXTRA_NVCC_FLAGS", "").split()
+        cmd = [nvcc, *NVCC_FLAGS, *extra, "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
