@@ -209,76 +209,92 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
   // ahead of their use, the blended entries' surfel indices and pixel masks three steps ahead,
   // their records one step ahead (into registers) - every load's address comes from a load
   // issued at least two steps earlier, so its L2 latency sits under the work in between.
-  auto load_words = [&](int c, uint32_t &wa, uint32_t &wb) {
-    wa = (c >= 0 && c <= top_a) ? words_a[c] : 0u;
-    wb = (c >= 0 && c <= top_b) ? words_b[c] : 0u;
-  };
-  auto load_entry = [&](int c, uint32_t wa, uint32_t wb, uint32_t &id, uint32_t &mask) {
-    id = 0u;
-    mask = 0u;
-    if (((wa | wb) >> lane) & 1u) {
-      const uint32_t q = ((uint32_t)c << 5) + lane;
-      id = min(plist[q], P - 1u);
-      if ((wa >> lane) & 1u) mask = pm_a[q];
-      if ((wb >> lane) & 1u) mask |= (uint32_t)pm_b[q] << 16;
-    }
-  };
-  uint32_t w0a, w0b, w1a, w1b, w2a, w2b, w3a, w3b;  // words of chunk .. chunk - 3
-  load_words(chunk, w0a, w0b);
-  load_words(chunk - 1, w1a, w1b);
-  load_words(chunk - 2, w2a, w2b);
-  load_words(chunk - 3, w3a, w3b);
-  uint32_t id0, mask0, id1, mask1, id2, mask2;      // entries of chunk .. chunk - 2
-  load_entry(chunk, w0a, w0b, id0, mask0);
-  load_entry(chunk - 1, w1a, w1b, id1, mask1);
-  load_entry(chunk - 2, w2a, w2b, id2, mask2);
+  // A warp issues in order, so ANY instruction that reads a register with a load in flight
+  // stalls it - a move included.  The four stages therefore keep the RAW loaded words (they
+  // are combined only when their step comes) in four fixed register sets whose roles rotate:
+  // the step body is instantiated once per rotation and nothing is shifted.
+  struct WalkStage { uint32_t wa, wb, idr, mar, mbr; };
+  WalkStage s0, s1, s2, s3;
+#define LOAD_WORDS(S, c)                                                 \
+  {                                                                      \
+    const int c_ = (c);                                                  \
+    S.wa = (c_ >= 0 && c_ <= top_a) ? words_a[c_] : 0u;                  \
+    S.wb = (c_ >= 0 && c_ <= top_b) ? words_b[c_] : 0u;                  \
+  }
+#define LOAD_ENTRY(S, c)                                                 \
+  {                                                                      \
+    S.idr = 0u; S.mar = 0u; S.mbr = 0u;                                  \
+    if (((S.wa | S.wb) >> lane) & 1u) {                                  \
+      const uint32_t q_ = ((uint32_t)(c) << 5) + lane;                   \
+      S.idr = plist[q_];                                                 \
+      if ((S.wa >> lane) & 1u) S.mar = pm_a[q_];                         \
+      if ((S.wb >> lane) & 1u) S.mbr = pm_b[q_];                         \
+    }                                                                    \
+  }
+  LOAD_WORDS(s0, chunk);
+  LOAD_WORDS(s1, chunk - 1);
+  LOAD_WORDS(s2, chunk - 2);
+  LOAD_WORDS(s3, chunk - 3);
+  LOAD_ENTRY(s0, chunk);
+  LOAD_ENTRY(s1, chunk - 1);
+  LOAD_ENTRY(s2, chunk - 2);
   float4 ra, rb, rc, rd;                            // records of chunk
   ra = rb = rc = rd = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (((w0a | w0b) >> lane) & 1u) {
-    const float4 *r = rec + 4 * (size_t)id0;
+  if (((s0.wa | s0.wb) >> lane) & 1u) {
+    const float4 *r = rec + 4 * (size_t)min(s0.idr, P - 1u);
     ra = __ldg(r); rb = __ldg(r + 1); rc = __ldg(r + 2); rd = __ldg(r + 3);
   }
-  int nent = 0;
+  int nent = 0, rot = 0;
   uint32_t pending = 0;
   __syncwarp();
+
+  // One step of the gather.  A: the stage of `chunk` (consumed, then re-armed for chunk - 4),
+  // B: chunk - 1 (its records are requested), D: chunk - 3 (its entries are requested).
+#define GATHER_STEP(A, B, C, D)                                                                  \
+  {                                                                                              \
+    const uint32_t vote = A.wa | A.wb;                                                           \
+    const uint32_t id = min(A.idr, P - 1u), mask = A.mar | (A.mbr << 16);                        \
+    const float4 a = ra, b = rb, c = rc, d = rd;                                                 \
+    LOAD_WORDS(A, chunk - 4);                                                                    \
+    LOAD_ENTRY(D, chunk - 3);                                                                    \
+    if (((B.wa | B.wb) >> lane) & 1u) {                                                          \
+      const float4 *r = rec + 4 * (size_t)min(B.idr, P - 1u);                                    \
+      ra = __ldg(r); rb = __ldg(r + 1); rc = __ldg(r + 2); rd = __ldg(r + 3);                    \
+    }                                                                                            \
+    if (vote) {                                                                                  \
+      const bool any = (vote >> lane) & 1u;                                                      \
+      const int ns = __popc(vote);                                                               \
+      if (any) {                                                                                 \
+        const int slot = nent + __popc(vote >> lane) - 1; /* later entries first */              \
+        st.ent_id[slot] = id;                                                                    \
+        st.ent_pos[slot] = ((uint32_t)chunk << 5) + lane;                                        \
+        st.ent_mask[slot] = mask;                                                                \
+        st.rec[slot][0] = a; st.rec[slot][1] = b; st.rec[slot][2] = c; st.rec[slot][3] = d;      \
+      }                                                                                          \
+      __syncwarp();                                                                              \
+      /* lay the entries' pairs end to end: every pixel's lane appends itself */                 \
+      for (int k = 0; k < ns; k++) {                                                             \
+        const int slot = nent + k;                                                               \
+        const uint32_t m = st.ent_mask[slot];                                                    \
+        if (lane == 0) st.ent_prefix[slot] = pending;                                            \
+        if ((m >> lane) & 1u) st.queue[pending + __popc(m & lt)] = (uint16_t)((slot << 5) | lane); \
+        pending += __popc(m);                                                                    \
+      }                                                                                          \
+      nent += ns;                                                                                \
+    }                                                                                            \
+    chunk--;                                                                                     \
+  }
 
   while (true) {
     // ---- gather blended entries, back to front, until they hold enough pairs ----
     while (chunk >= 0 && pending < GATHER_PAIRS && nent + 32 <= ENT_CAP) {
-      const uint32_t vote = w0a | w0b;
-      const uint32_t id = id0, mask = mask0;
-      const float4 a = ra, b = rb, c = rc, d = rd;
-      // advance the pipeline
-      w0a = w1a; w0b = w1b; w1a = w2a; w1b = w2b; w2a = w3a; w2b = w3b;
-      load_words(chunk - 4, w3a, w3b);
-      id0 = id1; mask0 = mask1; id1 = id2; mask1 = mask2;
-      load_entry(chunk - 3, w2a, w2b, id2, mask2);
-      if (((w0a | w0b) >> lane) & 1u) {
-        const float4 *r = rec + 4 * (size_t)id0;
-        ra = __ldg(r); rb = __ldg(r + 1); rc = __ldg(r + 2); rd = __ldg(r + 3);
+      switch (rot) {
+        case 0: GATHER_STEP(s0, s1, s2, s3); break;
+        case 1: GATHER_STEP(s1, s2, s3, s0); break;
+        case 2: GATHER_STEP(s2, s3, s0, s1); break;
+        default: GATHER_STEP(s3, s0, s1, s2); break;
       }
-      if (vote) {
-        const bool any = (vote >> lane) & 1u;
-        const int ns = __popc(vote);
-        if (any) {
-          const int slot = nent + __popc(vote >> lane) - 1;     // later entries first
-          st.ent_id[slot] = id;
-          st.ent_pos[slot] = ((uint32_t)chunk << 5) + lane;
-          st.ent_mask[slot] = mask;
-          st.rec[slot][0] = a; st.rec[slot][1] = b; st.rec[slot][2] = c; st.rec[slot][3] = d;
-        }
-        __syncwarp();
-        // lay the entries' pairs end to end: every pixel's lane appends itself
-        for (int k = 0; k < ns; k++) {
-          const int slot = nent + k;
-          const uint32_t m = st.ent_mask[slot];
-          if (lane == 0) st.ent_prefix[slot] = pending;
-          if ((m >> lane) & 1u) st.queue[pending + __popc(m & lt)] = (uint16_t)((slot << 5) | lane);
-          pending += __popc(m);
-        }
-        nent += ns;
-      }
-      chunk--;
+      rot = (rot + 1) & 3;
     }
     if (pending == 0) {
       if (chunk < 0) break;
@@ -416,6 +432,10 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
   if (lane == 0 && blockIdx.x < 8192) g_btrace[blockIdx.x][1] = btime();
 #endif
 }
+
+#undef GATHER_STEP
+#undef LOAD_ENTRY
+#undef LOAD_WORDS
 
 // Per-surfel VJP: dL/dT, dL/dnormal -> dL/dmean3D, dL/dscale, dL/dquat.
 // Writes every output element (zeros for culled surfels) so no memset is needed.

@@ -46,6 +46,14 @@ for s in secs:
             stall_tot[k] = stall_tot.get(k, 0) + v
         lines.append((num(r[ci["Instructions Executed"]]), num(r[ci["# Samples"]]),
                       s["file"].split("/")[-1], r[0], r[1].strip(), st))
+merged = {}          # several launches of the kernel in one report: one row per source line
+for inst, smp, f, ln, src, st in lines:
+    m = merged.setdefault((f, ln), [0, 0, f, ln, src, {}])
+    m[0] += inst
+    m[1] += smp
+    for k, v in st.items():
+        m[5][k] = m[5].get(k, 0) + v
+lines = [tuple(m) for m in merged.values()]
 ti, ts = sum(x[0] for x in lines), sum(x[1] for x in lines)
 print(f"# {rep}: {which}: {ti} warp instructions, {ts} stall samples")
 print("# stall reasons (share of samples): " +
