@@ -29,6 +29,11 @@
 #include "raster_math.cuh"
 
 #ifdef RENDER_TRACE
+__device__ unsigned long long g_bstage[8192][5];   // cycles in gather / P1 / P2 / P3 / reduce
+extern "C" __attribute__((visibility("default"))) int splat_debug_bwd_stages(unsigned long long *out) {
+  return (int)cudaMemcpyFromSymbol(out, g_bstage, sizeof(g_bstage));
+}
+#define STAGE_CLOCK(acc) { const long long c_ = clock64(); acc += c_ - t_stage; t_stage = c_; }
 __device__ unsigned long long g_btrace[8192][4];
 extern "C" __attribute__((visibility("default"))) int splat_debug_bwd_trace(unsigned long long *out) {
   return (int)cudaMemcpyFromSymbol(out, g_btrace, sizeof(g_btrace));
@@ -38,6 +43,10 @@ __device__ __forceinline__ unsigned long long btime() {
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
+#endif
+
+#ifndef RENDER_TRACE
+#define STAGE_CLOCK(acc)
 #endif
 
 namespace {
@@ -107,10 +116,7 @@ struct __align__(16) WarpStage {
   float pa[32], pd[32];             // P1 -> P2: alpha, depth of the batch's pairs
   uint32_t pe[32];                  // P1 -> P2: entry slot of the pair
   uint32_t pmask[32];               // per pixel: which lanes of the batch hold its pairs
-  float vbuf[32][13];               // P3: the pairs' 13 contributions, summed per entry
   uint16_t queue[QUEUE_CAP];        // the gathered pairs, (slot << 5) | pixel, back to front
-  float *dst_base[13];              // where component c of surfel 0 accumulates ...
-  uint32_t dst_stride[13];          // ... and the stride to the next surfel
 };
 
 // One WARP per CTA = one 8x4 pixel block; CTAs in order of decreasing number of pairs.
@@ -196,11 +202,6 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
     pc.gReg = dL_dout[pix + 6 * HW];
   }
   st.gN[0][lane] = pc.gN0; st.gN[1][lane] = pc.gN1; st.gN[2][lane] = pc.gN2;
-  if (lane < 13) {   // components 0-8: dL_dtransMat rows (stride 12, 4 per row), 9-11: normal, 12: opacity
-    st.dst_base[lane] = lane < 9 ? dL_dtransMat + (lane / 3) * 4 + (lane % 3)
-                                 : (lane < 12 ? dL_dnormal + (lane - 9) : dL_dopacity);
-    st.dst_stride[lane] = lane < 9 ? 12u : (lane < 12 ? 3u : 1u);
-  }
 
   const int top_a = max_a ? (int)((max_a - 1) >> 5) : -1, top_b = max_b ? (int)((max_b - 1) >> 5) : -1;
   int chunk = (int)((max_last - 1) >> 5);
@@ -247,6 +248,9 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
   int nent = 0, rot = 0;
   uint32_t pending = 0;
   __syncwarp();
+#ifdef RENDER_TRACE
+  long long t_stage = clock64(), c_gather = 0, c_p1 = 0, c_p2 = 0, c_p3 = 0, c_red = 0;
+#endif
 
   // One step of the gather.  A: the stage of `chunk` (consumed, then re-armed for chunk - 4),
   // B: chunk - 1 (its records are requested), D: chunk - 3 (its entries are requested).
@@ -302,6 +306,7 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
     }
     if (lane == 0) st.ent_prefix[nent] = pending;
     __syncwarp();
+    STAGE_CLOCK(c_gather)
 
     // ---- composite the gathered pairs, 32 at a time ----
     for (uint32_t base = 0; base < pending; base += 32) {
@@ -326,6 +331,7 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
       __syncwarp();
       if (ok) atomicOr(&st.pmask[pixel], 1u << lane);
       __syncwarp();
+      STAGE_CLOCK(c_p1)
       // P2: every pixel's lane runs its recurrences over its pairs of the batch, in list order
       {
         uint32_t m = st.pmask[lane];
@@ -341,6 +347,7 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
         }
       }
       __syncwarp();
+      STAGE_CLOCK(c_p2)
       // P3: the pair's contribution to its surfel's 13 values
       {
         float v[13];
@@ -395,41 +402,46 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
             v[8] = gy * sn * inv_d2d + cw * s.twz;
           }
         }
+        STAGE_CLOCK(c_p3)
+        // The batch's pairs of one entry sit in consecutive lanes: a segmented reduction by
+        // shuffles (13 independent chains, no shared-memory round trip) leaves every entry's
+        // sums in the first lane of its segment, which issues the 13 atomics.
 #pragma unroll
-        for (int i = 0; i < 13; i++) st.vbuf[lane][i] = v[i];
-      }
-      __syncwarp();
-      // the batch's pairs of one entry are consecutive: sum them per (entry, component)
-      {
-        const int nvalid = (int)min(32u, pending - base);
-        const int j_first = __shfl_sync(full, j, 0), j_last = __shfl_sync(full, j, nvalid - 1);
-        const int tasks = (j_last - j_first + 1) * 13;
-        for (int t = lane; t < tasks; t += 32) {
-          const int seg = t / 13, comp = t - seg * 13;
-          const int e = j_first + seg;
-          const int q0 = max((int)st.ent_prefix[e] - (int)base, 0);
-          const int q1 = min((int)st.ent_prefix[e + 1] - (int)base, nvalid);
-          float s0 = 0.0f, s1 = 0.0f;
-          int q = q0;
-          for (; q + 1 < q1; q += 2) {
-            s0 += st.vbuf[q][comp];
-            s1 += st.vbuf[q + 1][comp];
+        for (int d = 1; d < 32; d <<= 1) {
+          const int jd = __shfl_down_sync(full, j, d);
+          const bool take = lane + d < 32 && jd == j;
+#pragma unroll
+          for (int i = 0; i < 13; i++) {
+            const float o = __shfl_down_sync(full, v[i], d);
+            if (take) v[i] += o;
           }
-          if (q < q1) s0 += st.vbuf[q][comp];
-          const float sum = s0 + s1;
-          if (sum != 0.0f) {
-            atomicAdd(st.dst_base[comp] + (size_t)st.ent_id[e] * st.dst_stride[comp], sum);
-          }
+        }
+        const int jp = __shfl_up_sync(full, j, 1);
+        if (valid && (lane == 0 || jp != j)) {
+          const size_t gid = st.ent_id[j];
+          float *tm = dL_dtransMat + gid * 12, *nr = dL_dnormal + gid * 3;
+#pragma unroll
+          for (int i = 0; i < 9; i++)
+            if (v[i] != 0.0f) atomicAdd(tm + (i / 3) * 4 + (i % 3), v[i]);
+#pragma unroll
+          for (int i = 0; i < 3; i++)
+            if (v[9 + i] != 0.0f) atomicAdd(nr + i, v[9 + i]);
+          if (v[12] != 0.0f) atomicAdd(dL_dopacity + gid, v[12]);
         }
       }
       __syncwarp();
+      STAGE_CLOCK(c_red)
     }
     nent = 0;
     pending = 0;
     if (chunk < 0) break;
   }
 #ifdef RENDER_TRACE
-  if (lane == 0 && blockIdx.x < 8192) g_btrace[blockIdx.x][1] = btime();
+  if (lane == 0 && blockIdx.x < 8192) {
+    g_btrace[blockIdx.x][1] = btime();
+    g_bstage[blockIdx.x][0] = c_gather; g_bstage[blockIdx.x][1] = c_p1; g_bstage[blockIdx.x][2] = c_p2;
+    g_bstage[blockIdx.x][3] = c_p3;     g_bstage[blockIdx.x][4] = c_red;
+  }
 #endif
 }
 

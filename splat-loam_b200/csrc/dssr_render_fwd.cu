@@ -26,6 +26,11 @@
 #include "raster_math.cuh"
 
 #ifdef RENDER_TRACE
+__device__ unsigned long long g_rstage[8192][4];   // cycles in gather / evaluate / blend / write-down
+extern "C" __attribute__((visibility("default"))) int splat_debug_render_stages(unsigned long long *out) {
+  return (int)cudaMemcpyFromSymbol(out, g_rstage, sizeof(g_rstage));
+}
+#define STAGE_CLOCK(acc) { const long long c_ = clock64(); acc += c_ - t_stage; t_stage = c_; }
 __device__ unsigned long long g_rtrace[8192][4];
 extern "C" __attribute__((visibility("default"))) int splat_debug_render_trace(unsigned long long *out) {
   return (int)cudaMemcpyFromSymbol(out, g_rtrace, sizeof(g_rtrace));
@@ -35,6 +40,10 @@ __device__ __forceinline__ unsigned long long rtime() {
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
+#endif
+
+#ifndef RENDER_TRACE
+#define STAGE_CLOCK(acc)
 #endif
 
 namespace {
@@ -117,6 +126,7 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
 #ifdef RENDER_TRACE
   const unsigned long long t_start = rtime();
   uint32_t n_steps = 0, n_pairs = 0;
+  long long t_stage = clock64(), c_gather = 0, c_eval = 0, c_blend = 0, c_write = 0;
 #endif
   const uint32_t tile = tile_order ? tile_order[work / UNITS_PER_TILE] : work / UNITS_PER_TILE;
   const int unit = work % UNITS_PER_TILE;
@@ -272,6 +282,7 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
     n_pairs += pending;
 #endif
     __syncwarp();
+    STAGE_CLOCK(c_gather)
 
     // ---- evaluate and blend the queued pairs, 32 at a time ----
     for (uint32_t base = 0; base < pending; base += 32) {
@@ -296,6 +307,7 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
       __syncwarp();
       if (ok) atomicOr(&st.pmask[pixel], 1u << lane);
       __syncwarp();
+      STAGE_CLOCK(c_eval)
       // every pixel's own lane blends its pairs of the batch, in list order
       {
         uint32_t m = st.pmask[lane];
@@ -314,6 +326,7 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
         }
       }
       __syncwarp();
+      STAGE_CLOCK(c_blend)
       if (__all_sync(full, ps.done)) break;
     }
 
@@ -340,6 +353,7 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
       words_b[step0 + lane] = st.word_b[lane];
     }
     __syncwarp();
+    STAGE_CLOCK(c_write)
   }
 
 #ifdef RENDER_TRACE
@@ -348,6 +362,8 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
     g_rtrace[work][1] = rtime();
     g_rtrace[work][2] = ((unsigned long long)n_steps << 32) | n_pairs;
     g_rtrace[work][3] = range.y - range.x;
+    g_rstage[work][0] = c_gather; g_rstage[work][1] = c_eval;
+    g_rstage[work][2] = c_blend;  g_rstage[work][3] = c_write;
   }
 #endif
   // what the backward will have to do for this block: the number of blended (pixel, entry)

@@ -41,3 +41,10 @@ heapq.heapify(slots)
 for d in sorted(dur, reverse=True):
     heapq.heappush(slots, heapq.heappop(slots) + d)
 print("LPT list-scheduling makespan with measured durations: %.1f us" % max(slots))
+
+sb = np.zeros((8192, 5), dtype=np.uint64)
+if hasattr(n.load(), "splat_debug_bwd_stages") and n.load().splat_debug_bwd_stages(sb.ctypes.data_as(ctypes.c_void_p)) == 0:
+    sb = sb.astype(np.float64)
+    sb = sb[sb.sum(axis=1) > 0]
+    sh = sb / sb.sum(axis=1, keepdims=True)
+    print("stage share of a warp's cycles (mean over warps): gather %.2f P1 %.2f P2 %.2f P3 %.2f reduce %.2f" % tuple(sh.mean(axis=0)))

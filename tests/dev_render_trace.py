@@ -32,3 +32,13 @@ print("us per step (all): %.3f ; us per pair-step: %.3f" % (dur.sum() / steps.su
 for q in (50, 100, 150, 200, 250):
     print(f"  warps still running at {q} us: {(end > q).sum()}", end=";")
 print()
+
+# where a warp's time goes (clock64 between the stage boundaries, -DRENDER_TRACE build)
+sb = np.zeros((8192, 4), dtype=np.uint64)
+if hasattr(n.load(), "splat_debug_render_stages") and n.load().splat_debug_render_stages(sb.ctypes.data_as(ctypes.c_void_p)) == 0:
+    sb = sb.astype(np.float64)[: len(t)]
+    tot = sb.sum(axis=1, keepdims=True) + 1e-9
+    sh = (sb / tot)
+    print("stage share of a warp's cycles (mean over warps): gather %.2f evaluate %.2f blend %.2f write-down %.2f" % tuple(sh.mean(axis=0)))
+    print("cycles per step: gather %.0f evaluate %.0f blend %.0f write-down %.0f ; steps %.0f pairs/step %.1f" % (
+        *(sb.sum(axis=0) / steps.sum()), steps.mean(), pairs.sum() / steps.sum()))
