@@ -54,8 +54,16 @@ namespace {
 constexpr int SUB = 4;                                            // 4x4 pixels per sub-tile
 constexpr int SUBS_PER_TILE = (SPLAT_TILE / SUB) * (SPLAT_TILE / SUB);   // 16
 constexpr int UNITS_PER_TILE = SUBS_PER_TILE / 2;                 // a warp = two sub-tiles
-constexpr int ENT_CAP = 64;        // blended entries staged per warp
-constexpr int GATHER_PAIRS = 64;   // entries are gathered until they hold this many pairs
+#ifndef COMPOSITE_ENT_CAP
+#define COMPOSITE_ENT_CAP 64
+#endif
+constexpr int ENT_CAP = COMPOSITE_ENT_CAP;        // blended entries staged per warp
+// (measured at C2, forward / backward us: 32 pairs 231 / 265, 64: 219 / 252, 96: 213 / 244, 128: 210 / 242;
+//  more staged entries than 64 cost residency: ENT_CAP 128 puts the forward in two waves, 295 us)
+#ifndef COMPOSITE_GATHER_PAIRS
+#define COMPOSITE_GATHER_PAIRS 128
+#endif
+constexpr int GATHER_PAIRS = COMPOSITE_GATHER_PAIRS;   // entries are gathered until they hold this many pairs
 constexpr int QUEUE_CAP = GATHER_PAIRS + 32 * 32;   // one more step can add 32 entries x 32 pixels
 
 // Per-pixel state of the reverse traversal (backward.cu:62-98) and its constants.
