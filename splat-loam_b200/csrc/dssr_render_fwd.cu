@@ -108,9 +108,9 @@ struct __align__(16) FwdStage {
   uint32_t ent_mask[ENT_CAP];    // pixels that blended the entry (bit = lane of the pixel)
   uint32_t word_a[STEP_CAP], word_b[STEP_CAP];   // the phase's step words, per sub-tile
   float ray[10][32];             // per pixel: X Y Z ax ay ex ey ez pxf pyf
-  float pa[32], pd[32];          // evaluate -> blend: alpha (0: the pair failed), depth
-  uint32_t pe[32];               // evaluate -> blend: entry slot of the pair
-  uint32_t pmask[32];            // per pixel: which lanes of the batch hold its pairs
+  float pa[64], pd[64];          // evaluate -> blend: alpha, depth of the two batches' pairs
+  uint32_t pe[64];               // evaluate -> blend: entry slot of the pair
+  uint32_t pmask[64];            // per batch and pixel: which lanes of the batch hold its pairs
   uint16_t queue[QUEUE_CAP];     // (slot << 5) | pixel, in list order
 };
 
@@ -292,36 +292,54 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
     __syncwarp();
     STAGE_CLOCK(c_gather)
 
-    // ---- evaluate and blend the queued pairs, 32 at a time ----
-    for (uint32_t base = 0; base < pending; base += 32) {
-      const uint32_t g = base + lane;
-      const bool valid = g < pending;
-      const uint32_t item = valid ? st.queue[g] : (uint32_t)lane;
-      const int slot = item >> 5, pixel = item & 31;
-      const SurfelRec s = unpack_rec(st.rec[slot][0], st.rec[slot][1], st.rec[slot][2],
-                                     st.rec[slot][3]);
-      PixelRay ray;
-      ray.X = st.ray[0][pixel];  ray.Y = st.ray[1][pixel];  ray.Z = st.ray[2][pixel];
-      ray.ax = st.ray[3][pixel]; ray.ay = st.ray[4][pixel];
-      ray.ex = st.ray[5][pixel]; ray.ey = st.ray[6][pixel]; ray.ez = st.ray[7][pixel];
-      ray.pxf = st.ray[8][pixel]; ray.pyf = st.ray[9][pixel];
-      Hit h;
-      const bool ok = valid && intersect_begin(ray, s, st.cut[slot], h) &&
-                      intersect_finish(ray, s, h);
-      st.pa[lane] = ok ? h.alpha : 0.0f;
-      st.pd[lane] = ok ? h.depth : 0.0f;
-      st.pe[lane] = (uint32_t)slot;
-      st.pmask[lane] = 0u;
+    // ---- evaluate and blend the queued pairs, 64 at a time ----
+    // Two pairs per lane (g and g + 32), evaluated by the same straight-line code side by side:
+    // the two intersection chains are independent, which doubles the instruction-level
+    // parallelism of the stage that is bound by the latency of its dependent FP32 chain.
+    for (uint32_t base = 0; base < pending; base += 64) {
+      bool ok[2];
+      float alpha[2], depth[2];
+      int slot[2], pixel[2];
+#pragma unroll
+      for (int u = 0; u < 2; u++) {
+        const uint32_t g = base + 32 * u + lane;
+        const bool valid = g < pending;
+        const uint32_t item = valid ? st.queue[g] : (uint32_t)lane;
+        slot[u] = item >> 5;
+        pixel[u] = item & 31;
+        const SurfelRec s = unpack_rec(st.rec[slot[u]][0], st.rec[slot[u]][1], st.rec[slot[u]][2],
+                                       st.rec[slot[u]][3]);
+        PixelRay ray;
+        ray.X = st.ray[0][pixel[u]];  ray.Y = st.ray[1][pixel[u]];  ray.Z = st.ray[2][pixel[u]];
+        ray.ax = st.ray[3][pixel[u]]; ray.ay = st.ray[4][pixel[u]];
+        ray.ex = st.ray[5][pixel[u]]; ray.ey = st.ray[6][pixel[u]]; ray.ez = st.ray[7][pixel[u]];
+        ray.pxf = st.ray[8][pixel[u]]; ray.pyf = st.ray[9][pixel[u]];
+        Hit h;
+        // (branch-free: in a warp of 32 unrelated pairs an early exit is never taken by all)
+        ok[u] = intersect_all(ray, s, h) && valid;
+        alpha[u] = h.alpha;
+        depth[u] = h.depth;
+      }
+#pragma unroll
+      for (int u = 0; u < 2; u++) {
+        st.pa[32 * u + lane] = alpha[u];
+        st.pd[32 * u + lane] = depth[u];
+        st.pe[32 * u + lane] = (uint32_t)slot[u];
+        st.pmask[32 * u + lane] = 0u;
+      }
       __syncwarp();
-      if (ok) atomicOr(&st.pmask[pixel], 1u << lane);
+#pragma unroll
+      for (int u = 0; u < 2; u++)
+        if (ok[u]) atomicOr(&st.pmask[32 * u + pixel[u]], 1u << lane);
       __syncwarp();
       STAGE_CLOCK(c_eval)
-      // every pixel's own lane blends its pairs of the batch, in list order
-      {
-        uint32_t m = st.pmask[lane];
+      // every pixel's own lane blends its pairs of the two batches, in list order
+#pragma unroll
+      for (int u = 0; u < 2; u++) {
+        uint32_t m = st.pmask[32 * u + lane];
         while (__any_sync(full, m != 0u && !ps.done)) {
           if (m != 0u && !ps.done) {
-            const int q = __ffs(m) - 1;
+            const int q = 32 * u + __ffs(m) - 1;
             m &= m - 1u;
             const uint32_t e = st.pe[q];
             const float4 c = st.rec[e][2];
