@@ -382,6 +382,28 @@ SPLAT_API int gsa_photo_align(void *workspace, const gsa_photo_params *p,
                               const float *initial_guess, int iterations, float *transform,
                               float *stats, double *system);
 
+/* ---- range-image front end -------------------------------------------------------------
+ * Replaces Preprocessor.__call__ (scene/preprocessing.py:24-83, numpy + the `pyprojections`
+ * package on the CPU): a LiDAR cloud ([P,3] device) becomes the H x W spherical range image,
+ * normal image ([3,H,W], -p/|p| of the pixel's point) and valid mask of a Camera.
+ * PARITY UNPINNED: `pyprojections` (PyPI 0.0.3, pixi.toml:39) is not vendored with the reference
+ * and not in this image; the conventions (documented in csrc/range_image.cu) are the ones
+ * consistent with the camera matrix the reference ships in gsaligner/tests/data/K_ref.npy.
+ *   rimg_spherical_intrinsics  calculate_spherical_intrinsics: K from the cloud's azimuth /
+ *                              elevation extent; kept in the workspace and, if K_out != NULL,
+ *                              written as a row-major 3x3 (device);
+ *   rimg_project               Camera.project + the gathers: nearest return per pixel (ties to
+ *                              the smaller index); K = NULL uses the workspace's intrinsics,
+ *                              else a row-major 3x3 on the device; lut (int64 point index, -1
+ *                              where empty) is optional. */
+SPLAT_API size_t rimg_workspace_bytes(int H, int W);
+SPLAT_API int rimg_spherical_intrinsics(int P, const float *cloud, int H, int W, void *workspace,
+                                        float *K_out, void *stream);
+SPLAT_API int rimg_project(int P, const float *cloud, int H, int W, const float *K,
+                           float depth_min, float depth_max, void *workspace, long long *lut,
+                           float *range_image, float *normal_image, unsigned char *valid,
+                           void *stream);
+
 /* Number of kernels this library has launched so far in this process (all threads, all
  * devices).  No counterpart in the reference.  A harness takes the difference around a timed
  * region to report how many of the library's kernels ran in it. */

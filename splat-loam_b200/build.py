@@ -24,6 +24,7 @@ SOURCES = [
     "adam_step.cu",
     "state_surgery.cu",
     "photometric.cu",
+    "range_image.cu",
 ]
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-lineinfo",

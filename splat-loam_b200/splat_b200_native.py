@@ -128,6 +128,7 @@ EXPORTS = (
     "splat_compact_plan", "splat_compact_rows", "splat_append_rows",
     "gsa_photo_workspace_bytes", "gsa_photo_set_reference", "gsa_photo_set_query",
     "gsa_photo_align", "gsa_photo_debug_reference",
+    "rimg_workspace_bytes", "rimg_spherical_intrinsics", "rimg_project",
 )
 XCHG_HANDLE_BYTES = 64
 SURGERY_MAX_TENSORS = 12
@@ -228,6 +229,13 @@ def load():
                                     ctypes.c_int, ctypes.POINTER(fl), ctypes.POINTER(fl),
                                     ctypes.POINTER(ctypes.c_double)]
     lib.gsa_photo_align.restype = ctypes.c_int
+    lib.rimg_workspace_bytes.argtypes = [ctypes.c_int, ctypes.c_int]
+    lib.rimg_workspace_bytes.restype = ctypes.c_size_t
+    lib.rimg_spherical_intrinsics.argtypes = [ctypes.c_int, vp, ctypes.c_int, ctypes.c_int, vp, vp, vp]
+    lib.rimg_spherical_intrinsics.restype = ctypes.c_int
+    lib.rimg_project.argtypes = [ctypes.c_int, vp, ctypes.c_int, ctypes.c_int, vp, fl, fl, vp, vp, vp,
+                                 vp, vp, vp]
+    lib.rimg_project.restype = ctypes.c_int
     lib.splat_launch_count.argtypes = []
     lib.splat_launch_count.restype = ctypes.c_ulonglong
     for f in (lib.splat_xchg_create, lib.splat_xchg_export, lib.splat_xchg_connect,
