@@ -17,6 +17,9 @@
 // tile (two when there are more than 1024 tiles) — 4 passes of 8 B/instance instead
 // of CUB's 6 passes of 12 B/instance.  The last pass unpacks to the reference's
 // point_list_keys (u64) and point_list (u32), which are therefore bit-identical.
+#include <cstdlib>
+#include <cstring>
+
 #include "raster_math.cuh"
 
 namespace {
@@ -141,11 +144,13 @@ sort_pass_kernel(const unsigned long long *__restrict__ in, unsigned long long *
   const int bins = 1 << bits;
   uint16_t *s_cnt = reinterpret_cast<uint16_t *>(smem);            // [WARPS][bins]
   uint32_t *s_base = smem + (WARPS * bins) / 2;                    // [bins]
+  uint32_t *s_tbl = s_base + bins;                                 // [WARPS][bins]
   __shared__ uint32_t s_bid;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const uint32_t N = min(*num_ptr, capacity);
   if (tid == 0) s_bid = atomicAdd(ticket, 1u);
   for (int i = tid; i < (WARPS * bins) / 2; i += SORT_THREADS) smem[i] = 0u;
+  for (int i = tid; i < WARPS * bins; i += SORT_THREADS) s_tbl[i] = 0u;
   __syncthreads();
   const uint32_t bid = s_bid;
   const uint32_t start = bid * (SORT_THREADS * ITEMS);
@@ -156,25 +161,33 @@ sort_pass_kernel(const unsigned long long *__restrict__ in, unsigned long long *
   unsigned long long key[ITEMS];
   uint16_t rank[ITEMS];
   uint16_t *my_cnt = s_cnt + wid * bins;
+  uint32_t *my_tbl = s_tbl + wid * bins;
   const uint32_t wstart = start + wid * (ITEMS * 32);
 #pragma unroll
   for (int r = 0; r < ITEMS; r++) {
     uint32_t i = wstart + r * 32 + lane;
     key[r] = (i < N) ? in[i] : ~0ull;
   }
+  // The lanes of a warp that hold the same digit find each other through a per-warp table in
+  // shared memory (atomicOr of the lane bit, read back).  MATCH.ANY does it in one instruction
+  // but was measured at ~60 cycles per warp and SM on B200: 3x the time of this sequence.
 #pragma unroll
   for (int r = 0; r < ITEMS; r++) {
-    uint32_t i = wstart + r * 32 + lane;
-    bool valid = i < N;
-    uint32_t digit = valid ? ((uint32_t)(key[r] >> shift) & mask) : 0xffffffffu;
-    uint32_t peers = __match_any_sync(0xffffffffu, digit);
-    int leader = __ffs(peers) - 1;
-    uint32_t old = 0;
-    if (lane == leader && valid) {
+    const uint32_t i = wstart + r * 32 + lane;
+    const bool valid = i < N;
+    const uint32_t digit = (uint32_t)(key[r] >> shift) & mask;
+    if (valid) atomicOr(&my_tbl[digit], 1u << lane);
+    __syncwarp();
+    uint32_t peers = 0u, old = 0u;
+    if (valid) {
+      peers = my_tbl[digit];
       old = my_cnt[digit];
-      my_cnt[digit] = (uint16_t)(old + __popc(peers));
     }
-    old = __shfl_sync(0xffffffffu, old, leader);
+    __syncwarp();
+    if (valid && (peers & lt) == 0u) {         // the group's first lane
+      my_cnt[digit] = (uint16_t)(old + __popc(peers));
+      my_tbl[digit] = 0u;
+    }
     rank[r] = (uint16_t)(old + __popc(peers & lt));
     __syncwarp();
   }
@@ -248,7 +261,10 @@ __device__ __forceinline__ unsigned long long gtime() {
 //   * the unpacking to the reference's point_list_keys / point_list and the 16-bit
 //     sub-tile mask of every instance (previously a kernel of its own that re-read the keys)
 //     are done on the way out.
-template <int ITEMS>
+// UNPACK = false: the same pass as a plain stable partition - the words go out as words
+// (keys_out is then the destination word array); used to split the instances by tile BEFORE
+// their depth is sorted (tile_sort_kernel below).
+template <int ITEMS, bool UNPACK>
 __global__ void __launch_bounds__(SORT_THREADS)
 sort_last_pass_kernel(const unsigned long long *__restrict__ in,
                       unsigned long long *__restrict__ keys_out, uint32_t *__restrict__ plist_out,
@@ -262,12 +278,16 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
   uint32_t *s_loc = s_base + bins;                                 // [bins] CTA-local exclusive
   unsigned long long *s_stage =
       reinterpret_cast<unsigned long long *>(s_loc + bins);        // [(SORT_THREADS * ITEMS)]
+  // the ranking's per-warp peer table [WARPS][bins] lies over the staging area (used before
+  // it; the launch sizes the area for the larger of the two)
+  uint32_t *s_tbl = reinterpret_cast<uint32_t *>(s_stage);
   __shared__ uint32_t s_bid;
   __shared__ uint32_t s_warp[WARPS];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const uint32_t N = min(*num_ptr, capacity);
   if (tid == 0) s_bid = atomicAdd(ticket, 1u);
   for (int i = tid; i < (WARPS * bins) / 2; i += SORT_THREADS) smem[i] = 0u;
+  for (int i = tid; i < WARPS * bins; i += SORT_THREADS) s_tbl[i] = 0u;
   __syncthreads();
   const uint32_t bid = s_bid;
   const uint32_t start = bid * (SORT_THREADS * ITEMS);
@@ -280,6 +300,7 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
   unsigned long long key[ITEMS];
   uint16_t rank[ITEMS];
   uint16_t *my_cnt = s_cnt + wid * bins;
+  uint32_t *my_tbl = s_tbl + wid * bins;
   const uint32_t wstart = start + wid * (ITEMS * 32);
 #pragma unroll
   for (int r = 0; r < ITEMS; r++) {
@@ -301,23 +322,18 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
     const uint32_t i = wstart + r * 32 + lane;
     const bool valid = i < N;
     const uint32_t digit = (uint32_t)(key[r] >> shift) & mask;
-    uint32_t peers = __ballot_sync(0xffffffffu, valid);
-    peers = valid ? peers : ~peers;
-#pragma unroll
-    for (int b = 0; b < 10; b++) {          // SORT_MAX_BINS = 1024
-      if (b < bits) {
-        const bool bit = (digit >> b) & 1u;
-        const uint32_t m = __ballot_sync(0xffffffffu, bit);
-        peers &= bit ? m : ~m;
-      }
-    }
-    const int leader = __ffs(peers) - 1;
-    uint32_t old = 0;
-    if (lane == leader && valid) {
+    if (valid) atomicOr(&my_tbl[digit], 1u << lane);
+    __syncwarp();
+    uint32_t peers = 0u, old = 0u;
+    if (valid) {
+      peers = my_tbl[digit];
       old = my_cnt[digit];
-      my_cnt[digit] = (uint16_t)(old + __popc(peers));
     }
-    old = __shfl_sync(0xffffffffu, old, leader);
+    __syncwarp();
+    if (valid && (peers & lt) == 0u) {         // the group's first lane
+      my_cnt[digit] = (uint16_t)(old + __popc(peers));
+      my_tbl[digit] = 0u;
+    }
     rank[r] = (uint16_t)(old + __popc(peers & lt));
     __syncwarp();
   }
@@ -394,6 +410,14 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
   __syncthreads();
   TRACE(6)
 
+  if (!UNPACK) {
+    for (uint32_t j = tid; j < count; j += SORT_THREADS) {
+      const unsigned long long k = s_stage[j];
+      const uint32_t pos = j + s_base[(uint32_t)(k >> shift) & mask];
+      if (pos < capacity) keys_out[pos] = k;
+    }
+    return;
+  }
   const unsigned long long idx_mask = (1ull << idx_bits) - 1ull;
   bool cull_on = false;
   float inv_period = 0.0f;
@@ -444,6 +468,283 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
   TRACE(7)
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Tile-first sort (images of up to 1024 tiles).  The tile digit's histogram gives every tile's
+// range before anything is sorted, so the instance words are first split by tile with ONE
+// stable partition pass (sort_last_pass_kernel<.., false>) and each tile's range - a few
+// thousand words - is then sorted on its 27 depth bits by one CTA in shared memory: three
+// 9-bit LSD passes that never leave the SM, instead of three passes over all instances through
+// L2 with a chained scan each.  The write-out unpacks to the reference's point_list_keys /
+// point_list and computes the sub-tile masks, as the last global pass did.
+// Ranges longer than TS_CAP words are sorted by the same CTA with the same passes in global
+// memory (the tile's range of the two word arrays as ping and pong).
+#ifndef TS_EXP
+#define TS_EXP 0
+#endif
+constexpr int TS_THREADS = 1024;
+constexpr int TS_WARPS = TS_THREADS / 32;
+constexpr int TS_BINS = 512;
+constexpr int TS_ITEMS = 12;
+constexpr int TS_CAP = TS_THREADS * TS_ITEMS;
+// words | per-warp peer table (u32; the oversize path's u32 counts) | per-warp counts (u16) | scan
+constexpr size_t TS_SMEM = (size_t)TS_CAP * 8 + (size_t)TS_WARPS * TS_BINS * 4 +
+                           (size_t)TS_WARPS * TS_BINS * 2 + 3 * TS_BINS * 4;
+
+// counts -> offsets: cnt[w][d] becomes the number of words with digit d in warps before w,
+// s_base[d] the number of words with a smaller digit.  1024 threads: (digit, half of the warps).
+template <typename CT>
+__device__ __forceinline__ void ts_scan(CT *cnt, uint32_t *s_half, uint32_t *s_base,
+                                        uint32_t *s_warp) {
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int d = tid & (TS_BINS - 1), h = tid >> 9;
+  uint32_t c[16], run = 0;
+#pragma unroll
+  for (int j = 0; j < 16; j++) c[j] = cnt[(16 * h + j) * TS_BINS + d];
+#pragma unroll
+  for (int j = 0; j < 16; j++) {
+    const uint32_t t = c[j];
+    c[j] = run;
+    run += t;
+  }
+  s_half[h * TS_BINS + d] = run;
+  __syncthreads();
+  const uint32_t add = h ? s_half[d] : 0u;
+#pragma unroll
+  for (int j = 0; j < 16; j++) cnt[(16 * h + j) * TS_BINS + d] = (CT)(c[j] + add);
+  uint32_t tot = 0, inc = 0;
+  if (tid < TS_BINS) {
+    tot = s_half[tid] + s_half[TS_BINS + tid];
+    inc = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += n;
+    }
+    if (lane == 31) s_warp[wid] = inc;
+  }
+  __syncthreads();
+  if (tid < TS_BINS) {
+    uint32_t before = 0;
+    for (int w = 0; w < wid; w++) before += s_warp[w];
+    s_base[tid] = before + inc - tot;
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(TS_THREADS, 1)
+tile_sort_kernel(unsigned long long *words, unsigned long long *alt,
+                 const uint2 *__restrict__ ranges, const uint32_t *__restrict__ tile_order,
+                 uint32_t capacity, unsigned long long *__restrict__ keys_out,
+                 uint32_t *__restrict__ plist_out, MaskParams mp, uint32_t P, int idx_bits) {
+  extern __shared__ unsigned long long ts_smem[];
+  unsigned long long *s_buf = ts_smem;                                   // [TS_CAP]
+  uint32_t *tbl = reinterpret_cast<uint32_t *>(s_buf + TS_CAP);          // [TS_WARPS][TS_BINS]
+  uint16_t *cnt16 = reinterpret_cast<uint16_t *>(tbl + TS_WARPS * TS_BINS);   // [TS_WARPS][TS_BINS]
+  uint32_t *s_half = reinterpret_cast<uint32_t *>(cnt16 + TS_WARPS * TS_BINS);   // [2][TS_BINS]
+  uint32_t *s_base = s_half + 2 * TS_BINS;                               // [TS_BINS]
+  __shared__ uint32_t s_warp[32];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const uint32_t lt = (1u << lane) - 1u;
+  const uint32_t tile = tile_order ? tile_order[blockIdx.x] : blockIdx.x;
+  uint2 rg = ranges[tile];
+  rg.x = min(rg.x, capacity);          // only bites when the capacity hint was too small
+  rg.y = min(rg.y, capacity);
+  const uint32_t n = rg.y - rg.x;
+  if (n == 0) return;
+#ifdef SORT_TRACE
+  const uint32_t bid = blockIdx.x;
+  if (tid == 0 && bid < 1024) g_trace[bid][12] = n;
+#endif
+  TRACE(0)
+  const unsigned long long *fin;       // the sorted words of the tile
+
+  if (n <= (uint32_t)TS_CAP) {
+    // ---- the whole range in registers + shared memory ----
+    const int items = (int)((n + TS_THREADS - 1) / TS_THREADS);
+    const uint32_t wbase = (uint32_t)wid * items * 32;       // the warp's chunk, in list order
+    unsigned long long key[TS_ITEMS];
+    uint32_t rank[TS_ITEMS];
+    const unsigned long long *src = words + rg.x;
+#pragma unroll
+    for (int r = 0; r < TS_ITEMS; r++) {
+      const uint32_t i = wbase + r * 32 + lane;
+      key[r] = (r < items && i < n) ? src[i] : ~0ull;
+    }
+#ifdef SORT_TRACE
+    {
+      unsigned long long acc = 0;
+#pragma unroll
+      for (int r = 0; r < TS_ITEMS; r++) acc ^= key[r];
+      if (acc == 0xdeadbeefdeadbeefull) g_trace[0][15] = acc;
+    }
+#endif
+    TRACE(1)
+    // Ranking: the lanes of a warp that hold the same digit find each other through a
+    // per-warp table in shared memory (atomicOr of the lane bit, read back) - MATCH.ANY, which
+    // does the same in one instruction, was measured at ~60 cycles per warp and SM here: 7.4 us
+    // of every 10 us pass.
+    uint32_t *my_tbl = tbl + wid * TS_BINS;
+    uint16_t *my_cnt = cnt16 + wid * TS_BINS;
+    for (int i = tid; i < TS_WARPS * TS_BINS; i += TS_THREADS) tbl[i] = 0u;
+    for (int pass = 0; pass < 3; pass++) {
+      const int shift = idx_bits + 9 * pass;
+      for (int i = tid; i < TS_WARPS * TS_BINS / 2; i += TS_THREADS)
+        reinterpret_cast<uint32_t *>(cnt16)[i] = 0u;
+      __syncthreads();
+#pragma unroll
+      for (int r = 0; r < TS_ITEMS; r++) {
+        if (r < items) {
+          const uint32_t i = wbase + r * 32 + lane;
+          const bool valid = i < n;
+          const uint32_t digit = (uint32_t)(key[r] >> shift) & (TS_BINS - 1);
+          if (valid) atomicOr(&my_tbl[digit], 1u << lane);
+          __syncwarp();
+          uint32_t peers = 0u, old = 0u;
+          if (valid) {
+            peers = my_tbl[digit];
+            old = my_cnt[digit];
+          }
+          __syncwarp();
+          if (valid && (peers & lt) == 0u) {       // the group's first lane
+            my_cnt[digit] = (uint16_t)(old + __popc(peers));
+            my_tbl[digit] = 0u;
+          }
+          rank[r] = old + __popc(peers & lt);
+          __syncwarp();
+        }
+      }
+      __syncthreads();
+#ifdef SORT_TRACE
+      if (tid == 0 && bid < 1024) g_trace[bid][2 + 3 * pass] = gtime();
+#endif
+      ts_scan(cnt16, s_half, s_base, s_warp);
+#ifdef SORT_TRACE
+      if (tid == 0 && bid < 1024) g_trace[bid][3 + 3 * pass] = gtime();
+#endif
+#pragma unroll
+      for (int r = 0; r < TS_ITEMS; r++) {
+        if (r < items) {
+          const uint32_t i = wbase + r * 32 + lane;
+          if (i < n) {
+            const uint32_t digit = (uint32_t)(key[r] >> shift) & (TS_BINS - 1);
+            s_buf[s_base[digit] + my_cnt[digit] + rank[r]] = key[r];
+          }
+        }
+      }
+      __syncthreads();
+#ifdef SORT_TRACE
+      if (tid == 0 && bid < 1024) g_trace[bid][4 + 3 * pass] = gtime();
+#endif
+      if (pass < 2) {
+#pragma unroll
+        for (int r = 0; r < TS_ITEMS; r++) {
+          const uint32_t i = wbase + r * 32 + lane;
+          if (r < items && i < n) key[r] = s_buf[i];
+        }
+      }
+    }
+    fin = s_buf;
+  } else {
+    // ---- oversize range: the same three passes through global memory ----
+    uint32_t *cnt = tbl;
+    uint32_t *my_cnt = cnt + wid * TS_BINS;
+    unsigned long long *a = words + rg.x, *b = alt + rg.x;
+    const uint32_t chunk = ((n + TS_WARPS - 1) / TS_WARPS + 31u) & ~31u;
+    const uint32_t w0 = (uint32_t)wid * chunk, w1 = min(n, w0 + chunk);
+    for (int pass = 0; pass < 3; pass++) {
+      const int shift = idx_bits + 9 * pass;
+      for (int i = tid; i < TS_WARPS * TS_BINS; i += TS_THREADS) cnt[i] = 0u;
+      __syncthreads();
+      for (uint32_t i0 = w0; i0 < w1; i0 += 32) {
+        const uint32_t i = i0 + lane;
+        const bool valid = i < w1;
+        const uint32_t digit = valid ? ((uint32_t)(a[i] >> shift) & (TS_BINS - 1)) : 0xffffffffu;
+        const uint32_t peers = __match_any_sync(0xffffffffu, digit);
+        if (lane == __ffs(peers) - 1 && valid) my_cnt[digit] += __popc(peers);
+        __syncwarp();
+      }
+      __syncthreads();
+      ts_scan(cnt, s_half, s_base, s_warp);
+      for (uint32_t i0 = w0; i0 < w1; i0 += 32) {
+        const uint32_t i = i0 + lane;
+        const bool valid = i < w1;
+        const unsigned long long k = valid ? a[i] : 0ull;
+        const uint32_t digit = valid ? ((uint32_t)(k >> shift) & (TS_BINS - 1)) : 0xffffffffu;
+        const uint32_t peers = __match_any_sync(0xffffffffu, digit);
+        const int leader = __ffs(peers) - 1;
+        uint32_t old = 0;
+        if (lane == leader && valid) {
+          old = my_cnt[digit];
+          my_cnt[digit] = old + __popc(peers);
+        }
+        old = __shfl_sync(0xffffffffu, old, leader);
+        if (valid) b[s_base[digit] + old + __popc(peers & lt)] = k;
+        __syncwarp();
+      }
+      __threadfence_block();
+      __syncthreads();
+      unsigned long long *t = a;
+      a = b;
+      b = t;
+    }
+    fin = a;
+  }
+
+  // ---- write-out: the reference's arrays + the sub-tile masks ----
+  const unsigned long long idx_mask = (1ull << idx_bits) - 1ull;
+  bool cull_on = false;
+  float inv_period = 0.0f;
+  if (mp.sub_mask) {
+    const float fx = mp.projmatrix[0], fy = mp.projmatrix[5], cy = mp.projmatrix[9];
+    inv_period = 1.0f / (6.2831853f * fabsf(fx));
+    cull_on = fmaxf(fabsf((0.0f - cy) / fy), fabsf(((float)(mp.H - 1) - cy) / fy)) < 1.55f;
+  }
+  const float tx0 = (float)((tile % mp.tiles_x) * SPLAT_TILE), ty0 = (float)((tile / mp.tiles_x) * SPLAT_TILE);
+  constexpr int WU = 4;
+  for (uint32_t j0 = tid; j0 < n; j0 += WU * TS_THREADS) {
+    unsigned long long k[WU];
+    float4 cb[WU];
+#pragma unroll
+    for (int u = 0; u < WU; u++) {
+      const uint32_t j = j0 + u * TS_THREADS;
+      k[u] = j < n ? fin[j] : 0ull;
+    }
+#if TS_EXP == 2
+    for (int u = 0; u < WU; u++) cb[u] = make_float4(0.f, 100.f, 0.f, 100.f);
+#else
+    if (cull_on) {
+#pragma unroll
+      for (int u = 0; u < WU; u++)
+        cb[u] = __ldg(&mp.cull[min((uint32_t)(k[u] & idx_mask), P - 1u)]);
+    }
+#endif
+#pragma unroll
+    for (int u = 0; u < WU; u++) {
+      const uint32_t j = j0 + u * TS_THREADS;
+      if (j >= n) continue;
+      const uint32_t pos = rg.x + j;
+      const uint32_t idx = (uint32_t)(k[u] & idx_mask);
+      const uint32_t d27 = (uint32_t)(k[u] >> idx_bits) & ((1u << SPLAT_DEPTH_BITS) - 1u);
+      // (the tile bits of the word, not `tile`: identical except on the garbage a too-small
+      // capacity hint leaves behind, and then as the global pass would have written them)
+      const uint32_t wt = (uint32_t)(k[u] >> (idx_bits + SPLAT_DEPTH_BITS));
+      keys_out[pos] = ((unsigned long long)wt << 32) | (unsigned long long)(d27 + SPLAT_DEPTH_BASE);
+      plist_out[pos] = idx;
+      if (mp.sub_mask) {
+        uint32_t sm = 0xffffu;
+#if TS_EXP == 1
+        if (cull_on) sm = (uint32_t)cb[u].x;
+#else
+        if (cull_on) sm = subtile_mask(cb[u], tx0, ty0, inv_period);
+#endif
+        mp.sub_mask[pos] = (uint16_t)sm;
+      }
+    }
+  }
+  TRACE(11)
+}
+
 }  // namespace
 
 #ifdef SORT_TRACE
@@ -481,7 +782,8 @@ static int pick_items(uint32_t n_estimate) {
 }
 
 template <int ITEMS>
-static void launch_one_pass(bool last, const unsigned long long *src, unsigned long long *dst,
+static void launch_one_pass(int last /* 1: unpacking last pass, 2: staged partition */,
+                            const unsigned long long *src, unsigned long long *dst,
                             unsigned long long *keys_out, uint32_t *plist_out,
                             const MaskParams &mp, uint32_t P, const uint32_t *num_ptr,
                             uint32_t capacity, uint32_t *status, uint32_t *ticket,
@@ -490,21 +792,31 @@ static void launch_one_pass(bool last, const unsigned long long *src, unsigned l
   static unsigned long long seen = 0;
   if (first_use_on_device(seen)) {   // the widest pass (10 bits) needs more than the default 48 KB
     const int big = WARPS * SORT_MAX_BINS * 2 + SORT_MAX_BINS * 4;
-    cudaFuncSetAttribute(sort_pass_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
-    cudaFuncSetAttribute(sort_last_pass_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         big + SORT_MAX_BINS * 4 + SORT_THREADS * ITEMS * 8);
+    cudaFuncSetAttribute(sort_pass_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         big + WARPS * SORT_MAX_BINS * 4);
+    const int stage_max = SORT_THREADS * ITEMS * 8 > WARPS * SORT_MAX_BINS * 4
+                              ? SORT_THREADS * ITEMS * 8 : WARPS * SORT_MAX_BINS * 4;
+    cudaFuncSetAttribute(sort_last_pass_kernel<ITEMS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         big + SORT_MAX_BINS * 4 + stage_max);
+    cudaFuncSetAttribute(sort_last_pass_kernel<ITEMS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         big + SORT_MAX_BINS * 4 + stage_max);
   }
   const int nbins = 1 << bits;
   const int nblk = (int)(((size_t)capacity + SORT_THREADS * ITEMS - 1) / (SORT_THREADS * ITEMS));
   const size_t smem = (size_t)WARPS * nbins * 2 + (size_t)nbins * 4;
+  const size_t stage = (size_t)SORT_THREADS * ITEMS * 8 > (size_t)WARPS * nbins * 4
+                           ? (size_t)SORT_THREADS * ITEMS * 8 : (size_t)WARPS * nbins * 4;
   if (nblk < 1) return;
-  if (last)
-    sort_last_pass_kernel<ITEMS><<<nblk, SORT_THREADS,
-                                   smem + (size_t)nbins * 4 + (size_t)SORT_THREADS * ITEMS * 8, LS(s)>>>(
+  if (last == 1)
+    sort_last_pass_kernel<ITEMS, true><<<nblk, SORT_THREADS, smem + (size_t)nbins * 4 + stage, LS(s)>>>(
         src, keys_out, plist_out, mp, P, num_ptr, capacity, status, ticket, digit_base, shift, bits,
         idx_bits);
+  else if (last == 2)
+    sort_last_pass_kernel<ITEMS, false><<<nblk, SORT_THREADS, smem + (size_t)nbins * 4 + stage, LS(s)>>>(
+        src, dst, nullptr, mp, P, num_ptr, capacity, status, ticket, digit_base, shift, bits,
+        idx_bits);
   else
-    sort_pass_kernel<ITEMS><<<nblk, SORT_THREADS, smem, LS(s)>>>(src, dst, num_ptr, capacity, status,
+    sort_pass_kernel<ITEMS><<<nblk, SORT_THREADS, smem + (size_t)WARPS * nbins * 4, LS(s)>>>(src, dst, num_ptr, capacity, status,
                                                              ticket, digit_base, shift, bits);
 }
 
@@ -524,7 +836,7 @@ unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long
   const int items = pick_items(n_estimate ? n_estimate : capacity);
   const MaskParams none{};
   for (int p = 0; p < npass; p++) {
-    const bool last = unpack_last && p == npass - 1;
+    const int last = (unpack_last && p == npass - 1) ? 1 : 0;
 #define ONE_PASS(I)                                                                             \
   launch_one_pass<I>(last, src, dst, keys_out, plist_out, mp ? *mp : none, P, num_ptr, capacity, \
                      status + status_off[p], tickets + p, digit_base + p * SORT_MAX_BINS,        \
@@ -551,6 +863,31 @@ void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, con
   const int single = (sp.npass == 4) ? 3 : -1;
   launch_digit_scan(b.hist, b.digit_base, sp.npass, im.ranges, im.tile_order, im.tiles, single,
                     HIST_REPL, s);
+  // SPLAT_B200_SORT=global keeps the four global passes (developer A/B switch)
+  static const bool tile_first = [] {
+    const char *e = getenv("SPLAT_B200_SORT");
+    return !(e && strcmp(e, "global") == 0);
+  }();
+  if (single >= 0 && tile_first && im.tiles <= SPLAT_MAX_ORDERED_TILES) {
+    static unsigned long long seen = 0;
+    if (first_use_on_device(seen))
+      cudaFuncSetAttribute(tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TS_SMEM);
+    const int items = pick_items(n_estimate ? n_estimate : capacity);
+    const MaskParams none{};
+#define PART_PASS(I)                                                                              \
+  launch_one_pass<I>(2, b.words_a, b.words_b, nullptr, nullptr, none, (uint32_t)p.P,             \
+                     &g.hdr->num_rendered, capacity, b.status + b.status_off[single],            \
+                     b.tickets + single, b.digit_base + single * SORT_MAX_BINS, sp.shift[single], \
+                     sp.bits[single], sp.idx_bits, s)
+    if (items == 16) PART_PASS(16);
+    else if (items == 12) PART_PASS(12);
+    else PART_PASS(8);
+#undef PART_PASS
+    tile_sort_kernel<<<im.tiles, TS_THREADS, TS_SMEM, LS(s)>>>(
+        b.words_b, b.words_a, im.ranges, im.tile_order, capacity, b.keys, b.point_list, mp,
+        (uint32_t)p.P, sp.idx_bits);
+    return;
+  }
   launch_sort_passes(b.words_a, b.words_b, b.keys, b.point_list, &g.hdr->num_rendered,
                      capacity, b.status, b.status_off, b.tickets, b.digit_base, sp.npass,
                      sp.shift, sp.bits, 1, sp.idx_bits, n_estimate, s, &mp, (uint32_t)p.P);

@@ -187,3 +187,15 @@ def test_sort_with_16_keys_per_thread_matches_reference(native_lib, P):
     _compare(r, g, s["H"] * s["W"])
     r2 = _product(s)           # second frame: sized from the previous frame's count (hint path)
     _compare(r2, g, s["H"] * s["W"])
+
+
+def test_tile_ranges_longer_than_shared_memory_match_reference(native_lib):
+    """The tile-first sort keeps a tile's range in shared memory up to 12 288 instances and
+    sorts longer ranges through global memory: 8 tiles with ~40 000 instances each, plus the
+    hinted second frame."""
+    s = scenes.make_scene((32, 64, 45.0, 150000))
+    r, g = _product(s), _reference(s, backward=False)
+    lens = (g["ranges"].reshape(-1, 2).astype(np.int64) @ np.array([-1, 1]))
+    assert lens.max() > 12288 and lens.min() > 0, lens
+    _compare(r, g, s["H"] * s["W"])
+    _compare(_product(s), g, s["H"] * s["W"])
