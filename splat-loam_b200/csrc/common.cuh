@@ -298,6 +298,11 @@ void launch_emit(const FwdParams &p, const GeomView &g, const ImageView &im,
                  cudaStream_t s);
 void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, const BinView &b,
                  const SortPlan &sp, uint32_t capacity, uint32_t n_estimate, cudaStream_t s);
+// true: launch_sort takes the tile-first path (one partition pass by tile, then one CTA per
+// tile sorts the tile's range in shared memory); launch_emit then also writes every instance's
+// 16-bit sub-tile mask (into the `keys` array, which nothing else uses before the sort's last
+// kernel), and the partition pass packs it into the word's top 16 bits.
+bool sort_tile_first(const SortPlan &sp, int tiles);
 void launch_digit_scan(const uint32_t *hist, uint32_t *digit_base, int npass, uint2 *ranges,
                        uint32_t *tile_order, int tiles, int tile_pass_single, int nrepl,
                        cudaStream_t s);

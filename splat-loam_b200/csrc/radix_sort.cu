@@ -270,7 +270,8 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
                       unsigned long long *__restrict__ keys_out, uint32_t *__restrict__ plist_out,
                       MaskParams mp, uint32_t P, const uint32_t *__restrict__ num_ptr,
                       uint32_t capacity, uint32_t *status, uint32_t *ticket,
-                      const uint32_t *__restrict__ digit_base, int shift, int bits, int idx_bits) {
+                      const uint32_t *__restrict__ digit_base, int shift, int bits, int idx_bits,
+                      const uint16_t *__restrict__ mask_in) {
   extern __shared__ uint32_t smem[];
   const int bins = 1 << bits;
   uint16_t *s_cnt = reinterpret_cast<uint16_t *>(smem);            // [WARPS][bins]
@@ -281,6 +282,10 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
   // the ranking's per-warp peer table [WARPS][bins] lies over the staging area (used before
   // it; the launch sizes the area for the larger of the two)
   uint32_t *s_tbl = reinterpret_cast<uint32_t *>(s_stage);
+  // partition mode: the instances' sub-tile masks travel with the words
+  uint16_t *s_mask = reinterpret_cast<uint16_t *>(
+      reinterpret_cast<char *>(s_stage) +
+      (SORT_THREADS * ITEMS * 8 > WARPS * bins * 4 ? SORT_THREADS * ITEMS * 8 : WARPS * bins * 4));
   __shared__ uint32_t s_bid;
   __shared__ uint32_t s_warp[WARPS];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -306,6 +311,14 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
   for (int r = 0; r < ITEMS; r++) {
     uint32_t i = wstart + r * 32 + lane;
     key[r] = (i < N) ? in[i] : ~0ull;
+  }
+  uint16_t msk[UNPACK ? 1 : ITEMS];
+  if (!UNPACK) {
+#pragma unroll
+    for (int r = 0; r < ITEMS; r++) {
+      const uint32_t i = wstart + r * 32 + lane;
+      msk[r] = (i < N) ? mask_in[i] : (uint16_t)0;
+    }
   }
 #ifdef SORT_TRACE
   {
@@ -383,7 +396,9 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
     const uint32_t i = wstart + r * 32 + lane;
     if (i < N) {
       const uint32_t digit = (uint32_t)(key[r] >> shift) & mask;
-      s_stage[s_loc[digit] + my_cnt[digit] + rank[r]] = key[r];
+      const uint32_t slot = s_loc[digit] + my_cnt[digit] + rank[r];
+      s_stage[slot] = key[r];
+      if (!UNPACK) s_mask[slot] = msk[r];
     }
   }
   TRACE(4)
@@ -411,10 +426,12 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
   TRACE(6)
 
   if (!UNPACK) {
+    // the tile is the word's range from here on: its bits make room for the sub-tile mask
+    const unsigned long long low = (1ull << 48) - 1ull;
     for (uint32_t j = tid; j < count; j += SORT_THREADS) {
       const unsigned long long k = s_stage[j];
       const uint32_t pos = j + s_base[(uint32_t)(k >> shift) & mask];
-      if (pos < capacity) keys_out[pos] = k;
+      if (pos < capacity) keys_out[pos] = ((unsigned long long)s_mask[j] << 48) | (k & low);
     }
     return;
   }
@@ -479,9 +496,6 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
 // point_list and computes the sub-tile masks, as the last global pass did.
 // Ranges longer than TS_CAP words are sorted by the same CTA with the same passes in global
 // memory (the tile's range of the two word arrays as ping and pong).
-#ifndef TS_EXP
-#define TS_EXP 0
-#endif
 constexpr int TS_THREADS = 1024;
 constexpr int TS_WARPS = TS_THREADS / 32;
 constexpr int TS_BINS = 512;
@@ -691,56 +705,15 @@ tile_sort_kernel(unsigned long long *words, unsigned long long *alt,
     fin = a;
   }
 
-  // ---- write-out: the reference's arrays + the sub-tile masks ----
+  // ---- write-out: the reference's arrays; the sub-tile mask rides in the word's top bits ----
   const unsigned long long idx_mask = (1ull << idx_bits) - 1ull;
-  bool cull_on = false;
-  float inv_period = 0.0f;
-  if (mp.sub_mask) {
-    const float fx = mp.projmatrix[0], fy = mp.projmatrix[5], cy = mp.projmatrix[9];
-    inv_period = 1.0f / (6.2831853f * fabsf(fx));
-    cull_on = fmaxf(fabsf((0.0f - cy) / fy), fabsf(((float)(mp.H - 1) - cy) / fy)) < 1.55f;
-  }
-  const float tx0 = (float)((tile % mp.tiles_x) * SPLAT_TILE), ty0 = (float)((tile / mp.tiles_x) * SPLAT_TILE);
-  constexpr int WU = 4;
-  for (uint32_t j0 = tid; j0 < n; j0 += WU * TS_THREADS) {
-    unsigned long long k[WU];
-    float4 cb[WU];
-#pragma unroll
-    for (int u = 0; u < WU; u++) {
-      const uint32_t j = j0 + u * TS_THREADS;
-      k[u] = j < n ? fin[j] : 0ull;
-    }
-#if TS_EXP == 2
-    for (int u = 0; u < WU; u++) cb[u] = make_float4(0.f, 100.f, 0.f, 100.f);
-#else
-    if (cull_on) {
-#pragma unroll
-      for (int u = 0; u < WU; u++)
-        cb[u] = __ldg(&mp.cull[min((uint32_t)(k[u] & idx_mask), P - 1u)]);
-    }
-#endif
-#pragma unroll
-    for (int u = 0; u < WU; u++) {
-      const uint32_t j = j0 + u * TS_THREADS;
-      if (j >= n) continue;
-      const uint32_t pos = rg.x + j;
-      const uint32_t idx = (uint32_t)(k[u] & idx_mask);
-      const uint32_t d27 = (uint32_t)(k[u] >> idx_bits) & ((1u << SPLAT_DEPTH_BITS) - 1u);
-      // (the tile bits of the word, not `tile`: identical except on the garbage a too-small
-      // capacity hint leaves behind, and then as the global pass would have written them)
-      const uint32_t wt = (uint32_t)(k[u] >> (idx_bits + SPLAT_DEPTH_BITS));
-      keys_out[pos] = ((unsigned long long)wt << 32) | (unsigned long long)(d27 + SPLAT_DEPTH_BASE);
-      plist_out[pos] = idx;
-      if (mp.sub_mask) {
-        uint32_t sm = 0xffffu;
-#if TS_EXP == 1
-        if (cull_on) sm = (uint32_t)cb[u].x;
-#else
-        if (cull_on) sm = subtile_mask(cb[u], tx0, ty0, inv_period);
-#endif
-        mp.sub_mask[pos] = (uint16_t)sm;
-      }
-    }
+  for (uint32_t j = tid; j < n; j += TS_THREADS) {
+    const unsigned long long k = fin[j];
+    const uint32_t pos = rg.x + j;
+    const uint32_t d27 = (uint32_t)(k >> idx_bits) & ((1u << SPLAT_DEPTH_BITS) - 1u);
+    keys_out[pos] = ((unsigned long long)tile << 32) | (unsigned long long)(d27 + SPLAT_DEPTH_BASE);
+    plist_out[pos] = (uint32_t)(k & idx_mask);
+    if (mp.sub_mask) mp.sub_mask[pos] = (uint16_t)(k >> 48);
   }
   TRACE(11)
 }
@@ -788,7 +761,7 @@ static void launch_one_pass(int last /* 1: unpacking last pass, 2: staged partit
                             const MaskParams &mp, uint32_t P, const uint32_t *num_ptr,
                             uint32_t capacity, uint32_t *status, uint32_t *ticket,
                             const uint32_t *digit_base, int shift, int bits, int idx_bits,
-                            cudaStream_t s) {
+                            cudaStream_t s, const uint16_t *mask_in = nullptr) {
   static unsigned long long seen = 0;
   if (first_use_on_device(seen)) {   // the widest pass (10 bits) needs more than the default 48 KB
     const int big = WARPS * SORT_MAX_BINS * 2 + SORT_MAX_BINS * 4;
@@ -799,7 +772,7 @@ static void launch_one_pass(int last /* 1: unpacking last pass, 2: staged partit
     cudaFuncSetAttribute(sort_last_pass_kernel<ITEMS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          big + SORT_MAX_BINS * 4 + stage_max);
     cudaFuncSetAttribute(sort_last_pass_kernel<ITEMS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         big + SORT_MAX_BINS * 4 + stage_max);
+                         big + SORT_MAX_BINS * 4 + stage_max + SORT_THREADS * ITEMS * 2);
   }
   const int nbins = 1 << bits;
   const int nblk = (int)(((size_t)capacity + SORT_THREADS * ITEMS - 1) / (SORT_THREADS * ITEMS));
@@ -810,11 +783,13 @@ static void launch_one_pass(int last /* 1: unpacking last pass, 2: staged partit
   if (last == 1)
     sort_last_pass_kernel<ITEMS, true><<<nblk, SORT_THREADS, smem + (size_t)nbins * 4 + stage, LS(s)>>>(
         src, keys_out, plist_out, mp, P, num_ptr, capacity, status, ticket, digit_base, shift, bits,
-        idx_bits);
+        idx_bits, nullptr);
   else if (last == 2)
-    sort_last_pass_kernel<ITEMS, false><<<nblk, SORT_THREADS, smem + (size_t)nbins * 4 + stage, LS(s)>>>(
+    sort_last_pass_kernel<ITEMS, false><<<nblk, SORT_THREADS,
+                                          smem + (size_t)nbins * 4 + stage + (size_t)SORT_THREADS * ITEMS * 2,
+                                          LS(s)>>>(
         src, dst, nullptr, mp, P, num_ptr, capacity, status, ticket, digit_base, shift, bits,
-        idx_bits);
+        idx_bits, mask_in);
   else
     sort_pass_kernel<ITEMS><<<nblk, SORT_THREADS, smem + (size_t)WARPS * nbins * 4, LS(s)>>>(src, dst, num_ptr, capacity, status,
                                                              ticket, digit_base, shift, bits);
@@ -852,6 +827,18 @@ unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long
   return src;
 }
 
+// Tile-first needs the tile id in one digit (<= 1024 tiles) and 16 free bits above
+// [depth27 | idx] for the sub-tile mask (<= 2 M surfels); SPLAT_B200_SORT=global keeps the four
+// global passes (developer A/B switch).
+bool sort_tile_first(const SortPlan &sp, int tiles) {
+  static const bool enabled = [] {
+    const char *e = getenv("SPLAT_B200_SORT");
+    return !(e && strcmp(e, "global") == 0);
+  }();
+  return enabled && sp.npass == 4 && tiles <= SPLAT_MAX_ORDERED_TILES &&
+         sp.idx_bits + SPLAT_DEPTH_BITS + 16 <= 64;
+}
+
 void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, const BinView &b,
                  const SortPlan &sp, uint32_t capacity, uint32_t n_estimate, cudaStream_t s) {
   MaskParams mp;
@@ -863,12 +850,7 @@ void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, con
   const int single = (sp.npass == 4) ? 3 : -1;
   launch_digit_scan(b.hist, b.digit_base, sp.npass, im.ranges, im.tile_order, im.tiles, single,
                     HIST_REPL, s);
-  // SPLAT_B200_SORT=global keeps the four global passes (developer A/B switch)
-  static const bool tile_first = [] {
-    const char *e = getenv("SPLAT_B200_SORT");
-    return !(e && strcmp(e, "global") == 0);
-  }();
-  if (single >= 0 && tile_first && im.tiles <= SPLAT_MAX_ORDERED_TILES) {
+  if (sort_tile_first(sp, im.tiles)) {
     static unsigned long long seen = 0;
     if (first_use_on_device(seen))
       cudaFuncSetAttribute(tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TS_SMEM);
@@ -878,7 +860,7 @@ void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, con
   launch_one_pass<I>(2, b.words_a, b.words_b, nullptr, nullptr, none, (uint32_t)p.P,             \
                      &g.hdr->num_rendered, capacity, b.status + b.status_off[single],            \
                      b.tickets + single, b.digit_base + single * SORT_MAX_BINS, sp.shift[single], \
-                     sp.bits[single], sp.idx_bits, s)
+                     sp.bits[single], sp.idx_bits, s, reinterpret_cast<const uint16_t *>(b.keys))
     if (items == 16) PART_PASS(16);
     else if (items == 12) PART_PASS(12);
     else PART_PASS(8);
