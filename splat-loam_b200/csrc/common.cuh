@@ -27,6 +27,7 @@
 #define SPLAT_DEPTH_BITS 27       // bits(120.0f) - bits(0.1f) < 2^27
 #define SPLAT_ALPHA_MIN 0x3B808081u   // smallest float that is >= 1/255
 
+#define SPLAT_BLOCKS_PER_TILE 8    // 8x4-pixel blocks of a 16x16 tile (compositing work units)
 #define SPLAT_MAX_ORDERED_TILES 8192   // the O(tiles^2) work ordering is skipped beyond this
 
 #define PRE_CHUNK 256             // surfels per preprocess block (one thread each)
@@ -68,7 +69,7 @@ struct GeomLayout {
 };
 
 struct ImageLayout {
-  size_t final_T, n_contrib, ranges, tile_order, sub_cost, bwd_order, total;
+  size_t final_T, n_contrib, ranges, tile_order, sub_cost, bwd_order, blk_len, blk_top, total;
   int tiles_x, tiles_y, tiles;
   __host__ ImageLayout(int W, int H) {
     tiles_x = (W + SPLAT_TILE - 1) / SPLAT_TILE;
@@ -82,6 +83,8 @@ struct ImageLayout {
     tile_order = o; o = align_up(o + (size_t)tiles * 4, 256);
     sub_cost = o;  o = align_up(o + (size_t)tiles * 16 * 4, 256);   // per 4x4 sub-tile
     bwd_order = o; o = align_up(o + (size_t)tiles * 16 * 4, 256);
+    blk_len = o;   o = align_up(o + (size_t)tiles * SPLAT_BLOCKS_PER_TILE * 4, 256);
+    blk_top = o;   o = align_up(o + (size_t)tiles * SPLAT_BLOCKS_PER_TILE * 4, 256);
     total = o + 256;
   }
 };
@@ -124,18 +127,20 @@ struct BinHeader {
   // byte offset (from the aligned buffer start) of sub_mask: the backward only knows
   // num_rendered, not the capacity the forward laid the buffer out with
   unsigned long long off_sub_mask;
-  // what the forward compositing leaves for the backward (see dssr_render_fwd.cu): per 4x4
-  // sub-tile plane s (16 planes), blend_bits[s][bits_stride] holds one word per 32-entry step
-  // of the sub-tile's walk (bit i: entry i of the step was blended by some pixel) and
-  // pix_mask[s][capacity] the 16-bit mask of the pixels that blended each such entry
-  unsigned long long off_blend_bits, off_pix_mask;
-  uint32_t bits_stride, pix_stride;
+  // Block lists (block_list_kernel, radix_sort.cu): every 8x4 pixel block - the compositing
+  // kernels' unit of work, 8 per tile - has its own list of the tile's entries whose sub-tile
+  // mask touches it, in list order: blist[] = (surfel index, position in the tile's list).
+  // The list of block u of tile t starts at element 8 * ranges[t].x + u * (length of t's list).
+  // What the forward compositing leaves for the backward, indexed like blist: bpix[] = the
+  // 32-bit mask of the block's pixels that blended the entry; bwords[] = one word per 32
+  // entries (bit i: entry i of the step was blended by some pixel), the word of step k of the
+  // block at (start >> 5) + 8 * t + u + k.
+  unsigned long long off_blist, off_bpix, off_bwords;
 };
 
 struct BinLayout {
-  size_t words_a, words_b, keys, point_list, sub_mask, blend_bits, pix_mask, keys_unsorted, hist,
+  size_t words_a, words_b, keys, point_list, sub_mask, blist, bpix, bwords, keys_unsorted, hist,
       digit_base, status, tickets, total;
-  uint32_t bits_stride, pix_stride;
   size_t status_bytes, hist_bytes;
   size_t status_off[SORT_MAX_PASSES];  // element offset of each pass in `status`
   int nblk;
@@ -150,11 +155,11 @@ struct BinLayout {
     words_a = o;    o = align_up(o + C * 8, 256);
     words_b = o;    o = align_up(o + C * 8, 256);
     sub_mask = o;   o = align_up(o + C * 2, 256);
-    // a step word of tile t, step k lives at (range.x >> 5) + t + k: unique per (tile, step)
-    bits_stride = (uint32_t)((C >> 5) + (size_t)ntiles + 2);
-    pix_stride = (uint32_t)align_up(C, 128);
-    blend_bits = o; o = align_up(o + (size_t)16 * bits_stride * 4, 256);
-    pix_mask = o;   o = align_up(o + (size_t)16 * pix_stride * 2, 256);
+    // (worst case: every entry of a tile touches all 8 blocks)
+    blist = o;      o = align_up(o + C * SPLAT_BLOCKS_PER_TILE * 8, 256);
+    bpix = o;       o = align_up(o + C * SPLAT_BLOCKS_PER_TILE * 4, 256);
+    bwords = o;
+    o = align_up(o + ((C * SPLAT_BLOCKS_PER_TILE >> 5) + (size_t)ntiles * SPLAT_BLOCKS_PER_TILE + 2) * 4, 256);
     keys_unsorted = o;
     if (keep_unsorted) o = align_up(o + C * 8, 256);
     // [hist | tickets | status] are zeroed with ONE memset per forward
@@ -199,6 +204,8 @@ struct ImageView {
   uint32_t *tile_order;   // tiles sorted by decreasing list length (work scheduling)
   uint32_t *sub_cost;     // per sub-tile (tile * 16 + sub): list entries the forward consumed
   uint32_t *bwd_order;    // sub-tiles by decreasing sub_cost: the backward's CTA numbering
+  uint32_t *blk_len;      // per 8x4 block (tile * 8 + block): length of its list
+  uint32_t *blk_top;      // per block: 32-entry steps of its list the forward walked
   int tiles_x, tiles_y, tiles;
 };
 struct BinView {
@@ -206,10 +213,10 @@ struct BinView {
   unsigned long long *words_a, *words_b, *keys, *keys_unsorted;
   uint32_t *point_list;
   uint16_t *sub_mask;     // per sorted instance: which 4x4 sub-tiles of its tile it can touch
-  size_t off_sub_mask, off_blend_bits, off_pix_mask;
-  uint32_t *blend_bits;   // [16][bits_stride]
-  uint16_t *pix_mask;     // [16][pix_stride]
-  uint32_t bits_stride, pix_stride;
+  size_t off_sub_mask, off_blist, off_bpix, off_bwords;
+  uint2 *blist;           // per block: (surfel index, position in the tile's list)
+  uint32_t *bpix;         // per block-list entry: the pixels of the block that blended it
+  uint32_t *bwords;       // per 32 block-list entries: which were blended
   uint32_t *hist, *digit_base, *status, *tickets;
   size_t status_off[SORT_MAX_PASSES];
   size_t zero_bytes;  // [hist .. end of status) is one contiguous region to clear
@@ -242,6 +249,8 @@ static inline ImageView make_image_view(const char *buf, int W, int H) {
   v.tile_order = (uint32_t *)(b + L.tile_order);
   v.sub_cost = (uint32_t *)(b + L.sub_cost);
   v.bwd_order = (uint32_t *)(b + L.bwd_order);
+  v.blk_len = (uint32_t *)(b + L.blk_len);
+  v.blk_top = (uint32_t *)(b + L.blk_top);
   v.tiles_x = L.tiles_x;
   v.tiles_y = L.tiles_y;
   v.tiles = L.tiles;
@@ -260,12 +269,12 @@ static inline BinView make_bin_view(const char *buf, size_t C, int keep_unsorted
   v.point_list = (uint32_t *)(b + L.point_list);
   v.sub_mask = (uint16_t *)(b + L.sub_mask);
   v.off_sub_mask = L.sub_mask;
-  v.off_blend_bits = L.blend_bits;
-  v.off_pix_mask = L.pix_mask;
-  v.blend_bits = (uint32_t *)(b + L.blend_bits);
-  v.pix_mask = (uint16_t *)(b + L.pix_mask);
-  v.bits_stride = L.bits_stride;
-  v.pix_stride = L.pix_stride;
+  v.off_blist = L.blist;
+  v.off_bpix = L.bpix;
+  v.off_bwords = L.bwords;
+  v.blist = (uint2 *)(b + L.blist);
+  v.bpix = (uint32_t *)(b + L.bpix);
+  v.bwords = (uint32_t *)(b + L.bwords);
   v.hist = (uint32_t *)(b + L.hist);
   v.digit_base = (uint32_t *)(b + L.digit_base);
   v.status = (uint32_t *)(b + L.status);

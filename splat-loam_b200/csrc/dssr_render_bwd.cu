@@ -130,7 +130,7 @@ struct __align__(16) WarpStage {
 // One WARP per CTA = one 8x4 pixel block; CTAs in order of decreasing number of pairs.
 __global__ void __launch_bounds__(32, 14)
 render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restrict__ bwd_order,
-                       const uint32_t *__restrict__ point_list, const char *__restrict__ bin_base,
+                       const uint32_t *__restrict__ blk_top, const char *__restrict__ bin_base,
                        const BinHeader *__restrict__ bhdr, const float4 *__restrict__ rec,
                        const float *__restrict__ projmatrix, int W, int H, int tiles_x, uint32_t P,
                        const float *__restrict__ final_T, const uint32_t *__restrict__ n_contrib,
@@ -156,28 +156,23 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
   const size_t HW = (size_t)W * H;
   const size_t pix = (size_t)py * W + px;
 
-  // how far each sub-tile's forward walk got: the furthest entry one of its pixels blended
-  const uint32_t last_contributor = inside ? n_contrib[pix] : 0u;
-  uint32_t max_mine = last_contributor;
-#pragma unroll
-  for (int o = 8; o > 0; o >>= 1) max_mine = max(max_mine, __shfl_xor_sync(full, max_mine, o));
-  const uint32_t max_other = __shfl_xor_sync(full, max_mine, 16);
-  const uint32_t max_a = half ? max_other : max_mine, max_b = half ? max_mine : max_other;
-  const uint32_t max_last = max(max_a, max_b);
+  // how far the forward walked the block's list (in 32-entry steps)
+  const uint32_t top = blk_top[unit];
 #ifdef RENDER_TRACE
-  if (lane == 0 && blockIdx.x < 8192) g_btrace[blockIdx.x][2] = max_last;
+  if (lane == 0 && blockIdx.x < 8192) g_btrace[blockIdx.x][2] = top;
 #endif
-  if (max_last == 0) return;
+  if (top == 0) return;
 
-  const uint2 range = ranges[tile];
-  const uint32_t bits_stride = bhdr->bits_stride, pix_stride = bhdr->pix_stride;
-  const uint32_t *words_a = reinterpret_cast<const uint32_t *>(bin_base + bhdr->off_blend_bits) +
-                            (size_t)sub_a * bits_stride + (range.x >> 5) + tile;
-  const uint32_t *words_b = words_a + bits_stride;
-  const uint16_t *pm_a = reinterpret_cast<const uint16_t *>(bin_base + bhdr->off_pix_mask) +
-                         (size_t)sub_a * pix_stride + range.x;
-  const uint16_t *pm_b = pm_a + pix_stride;
-  const uint32_t *plist = point_list + range.x;
+  // the block's list and what the forward wrote down about it (dssr_render_fwd.cu)
+  uint2 range = ranges[tile];
+  range.x = min(range.x, bhdr->capacity);
+  range.y = min(range.y, bhdr->capacity);
+  const size_t ubase = (size_t)UNITS_PER_TILE * range.x +
+                       (size_t)(unit % UNITS_PER_TILE) * (range.y - range.x);
+  const uint2 *bl = reinterpret_cast<const uint2 *>(bin_base + bhdr->off_blist) + ubase;
+  const uint32_t *bw = reinterpret_cast<const uint32_t *>(bin_base + bhdr->off_bwords) +
+                       (ubase >> 5) + unit;
+  const uint32_t *bp = reinterpret_cast<const uint32_t *>(bin_base + bhdr->off_bpix) + ubase;
 
   const float fx = projmatrix[0], fy = projmatrix[5], cx = projmatrix[8], cy = projmatrix[9];
   {
@@ -211,33 +206,31 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
   }
   st.gN[0][lane] = pc.gN0; st.gN[1][lane] = pc.gN1; st.gN[2][lane] = pc.gN2;
 
-  const int top_a = max_a ? (int)((max_a - 1) >> 5) : -1, top_b = max_b ? (int)((max_b - 1) >> 5) : -1;
-  int chunk = (int)((max_last - 1) >> 5);
+  int chunk = (int)top - 1;
   const uint32_t lt = (1u << lane) - 1u;
   // Software pipeline of the walk (back to front): the step words are fetched four steps
-  // ahead of their use, the blended entries' surfel indices and pixel masks three steps ahead,
+  // ahead of their use, the blended entries' list entries and pixel masks three steps ahead,
   // their records one step ahead (into registers) - every load's address comes from a load
   // issued at least two steps earlier, so its L2 latency sits under the work in between.
   // A warp issues in order, so ANY instruction that reads a register with a load in flight
   // stalls it - a move included.  The four stages therefore keep the RAW loaded words (they
   // are combined only when their step comes) in four fixed register sets whose roles rotate:
   // the step body is instantiated once per rotation and nothing is shifted.
-  struct WalkStage { uint32_t wa, wb, idr, mar, mbr; };
+  struct WalkStage { uint32_t w, idr, posr, mr; };
   WalkStage s0, s1, s2, s3;
 #define LOAD_WORDS(S, c)                                                 \
   {                                                                      \
     const int c_ = (c);                                                  \
-    S.wa = (c_ >= 0 && c_ <= top_a) ? words_a[c_] : 0u;                  \
-    S.wb = (c_ >= 0 && c_ <= top_b) ? words_b[c_] : 0u;                  \
+    S.w = c_ >= 0 ? bw[c_] : 0u;                                         \
   }
 #define LOAD_ENTRY(S, c)                                                 \
   {                                                                      \
-    S.idr = 0u; S.mar = 0u; S.mbr = 0u;                                  \
-    if (((S.wa | S.wb) >> lane) & 1u) {                                  \
+    S.idr = 0u; S.posr = 0u; S.mr = 0u;                                  \
+    if ((S.w >> lane) & 1u) {                                            \
       const uint32_t q_ = ((uint32_t)(c) << 5) + lane;                   \
-      S.idr = plist[q_];                                                 \
-      if ((S.wa >> lane) & 1u) S.mar = pm_a[q_];                         \
-      if ((S.wb >> lane) & 1u) S.mbr = pm_b[q_];                         \
+      const uint2 e_ = bl[q_];                                           \
+      S.idr = e_.x; S.posr = e_.y;                                       \
+      S.mr = bp[q_];                                                     \
     }                                                                    \
   }
   LOAD_WORDS(s0, chunk);
@@ -249,7 +242,7 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
   LOAD_ENTRY(s2, chunk - 2);
   float4 ra, rb, rc, rd;                            // records of chunk
   ra = rb = rc = rd = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (((s0.wa | s0.wb) >> lane) & 1u) {
+  if ((s0.w >> lane) & 1u) {
     const float4 *r = rec + 4 * (size_t)min(s0.idr, P - 1u);
     ra = __ldg(r); rb = __ldg(r + 1); rc = __ldg(r + 2); rd = __ldg(r + 3);
   }
@@ -264,12 +257,12 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
   // B: chunk - 1 (its records are requested), D: chunk - 3 (its entries are requested).
 #define GATHER_STEP(A, B, C, D)                                                                  \
   {                                                                                              \
-    const uint32_t vote = A.wa | A.wb;                                                           \
-    const uint32_t id = min(A.idr, P - 1u), mask = A.mar | (A.mbr << 16);                        \
+    const uint32_t vote = A.w;                                                                   \
+    const uint32_t id = min(A.idr, P - 1u), mask = A.mr, pos = A.posr;                           \
     const float4 a = ra, b = rb, c = rc, d = rd;                                                 \
     LOAD_WORDS(A, chunk - 4);                                                                    \
     LOAD_ENTRY(D, chunk - 3);                                                                    \
-    if (((B.wa | B.wb) >> lane) & 1u) {                                                          \
+    if ((B.w >> lane) & 1u) {                                                                    \
       const float4 *r = rec + 4 * (size_t)min(B.idr, P - 1u);                                    \
       ra = __ldg(r); rb = __ldg(r + 1); rc = __ldg(r + 2); rd = __ldg(r + 3);                    \
     }                                                                                            \
@@ -279,7 +272,7 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
       if (any) {                                                                                 \
         const int slot = nent + __popc(vote >> lane) - 1; /* later entries first */              \
         st.ent_id[slot] = id;                                                                    \
-        st.ent_pos[slot] = ((uint32_t)chunk << 5) + lane;                                        \
+        st.ent_pos[slot] = pos;                                                                  \
         st.ent_mask[slot] = mask;                                                                \
         st.rec[slot][0] = a; st.rec[slot][1] = b; st.rec[slot][2] = c; st.rec[slot][3] = d;      \
       }                                                                                          \
@@ -578,7 +571,7 @@ void launch_render_backward(const BwdParams &p, const GeomView &g, const ImageVi
     cudaFuncSetAttribute(render_backward_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                          cudaSharedmemCarveoutMaxShared);
   render_backward_kernel<<<im.tiles * UNITS_PER_TILE, 32, 0, LS(s)>>>(
-      im.ranges, im.bwd_order, b.point_list, reinterpret_cast<const char *>(b.hdr), b.hdr, g.rec,
+      im.ranges, im.bwd_order, im.blk_top, reinterpret_cast<const char *>(b.hdr), b.hdr, g.rec,
       p.projmatrix, p.W, p.H, im.tiles_x, (uint32_t)p.P, im.final_T, im.n_contrib, p.dL_dout, p.dL_dtransMat, p.dL_dnormal, p.dL_dopacity);
 }
 

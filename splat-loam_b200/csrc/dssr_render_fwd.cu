@@ -7,11 +7,11 @@
 // depth-sorted list, evaluates every entry and the CTA leaves only when all 256 pixels are
 // done.  Here the unit of work is a WARP that owns an 8x4 pixel block (two 4x4 sub-tiles) and
 // walks its tile's list on its own, in three stages that each keep the 32 lanes busy:
-//   * gather: 32 list entries per step; the entries whose 16-bit sub-tile mask (written by the
-//     last sort pass from the surfel's conservative cull box) touches the block are staged in
-//     shared memory - 64-byte record and 16-byte cull box, 128-bit loads, L2-resident - and
-//     every pixel tests itself against each staged entry's cull box; the (pixel, entry) pairs
-//     that pass are appended to a queue, in list order;
+//   * gather: 32 entries of the BLOCK's list per step (block_list_kernel, radix_sort.cu: the
+//     tile's entries whose 16-bit sub-tile mask touches the block, a few per cent of the tile's
+//     list); they are staged in shared memory - 64-byte record and 16-byte cull box, 128-bit
+//     loads, L2-resident - and every pixel tests itself against each staged entry's cull box;
+//     the (pixel, entry) pairs that pass are appended to a queue, in list order;
 //   * evaluate: the queue is consumed 32 pairs at a time, ONE PAIR PER LANE whatever its pixel
 //     and entry: ray-splat intersection, alpha, depth (forward.cu:249-301);
 //   * blend: every pixel's own lane blends its pairs of the batch in list order
@@ -20,9 +20,9 @@
 // alpha >= 1/255 is possible, so such a pair is one the reference `continue`s over without
 // touching any state.  `contributor` keeps counting list positions, so n_contrib /
 // median_contributor are the reference's.
-// The kernel also writes down what it blended - per 32-entry step one word per sub-tile (which
-// entries) and per blended entry the 16-bit mask of the sub-tile's pixels - which is all the
-// backward needs to know (dssr_render_bwd.cu).
+// The kernel also writes down what it blended - per 32-entry step of the block's list one word
+// (which entries) and per blended entry the 32-bit mask of the block's pixels - which is all
+// the backward needs to know (dssr_render_bwd.cu).
 #include "raster_math.cuh"
 
 #ifdef RENDER_TRACE
@@ -106,7 +106,7 @@ struct __align__(16) FwdStage {
   float cut[ENT_CAP];            // conservative cutoff on rho for the entry's opacity
   uint32_t ent_pos[ENT_CAP];     // the reference's `contributor` (1-based list position)
   uint32_t ent_mask[ENT_CAP];    // pixels that blended the entry (bit = lane of the pixel)
-  uint32_t word_a[STEP_CAP], word_b[STEP_CAP];   // the phase's step words, per sub-tile
+  uint32_t word[STEP_CAP];       // the phase's step words
   float ray[10][32];             // per pixel: X Y Z ax ay ex ey ez pxf pyf
   float pa[64], pd[64];          // evaluate -> blend: alpha, depth of the two batches' pairs
   uint32_t pe[64];               // evaluate -> blend: entry slot of the pair
@@ -119,14 +119,14 @@ struct __align__(16) FwdStage {
 // of long and short lists.
 __global__ void __launch_bounds__(32, 16)
 render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restrict__ tile_order,
-                      const uint32_t *__restrict__ point_list,
-                      const uint16_t *__restrict__ sub_mask, const float4 *__restrict__ rec,
+                      const uint2 *__restrict__ blist, const uint32_t *__restrict__ blk_len,
+                      const float4 *__restrict__ rec,
                       const float4 *__restrict__ cull, const float *__restrict__ projmatrix, int W,
                       int H, int tiles_x, uint32_t capacity, uint32_t P,
                       float *__restrict__ final_T, uint32_t *__restrict__ n_contrib,
                       float *__restrict__ out, uint32_t *__restrict__ unit_cost,
-                      uint32_t *__restrict__ blend_bits, uint32_t bits_stride,
-                      uint16_t *__restrict__ pix_mask, uint32_t pix_stride) {
+                      uint32_t *__restrict__ blk_top, uint32_t *__restrict__ bwords,
+                      uint32_t *__restrict__ bpix) {
   __shared__ FwdStage st;
   const int lane = threadIdx.x, half = lane >> 4, p16 = lane & 15;
   const uint32_t full = 0xffffffffu;
@@ -142,7 +142,7 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
   const int x0 = (tile % tiles_x) * SPLAT_TILE + (sub_a & 3) * SUB;
   const int y0 = (tile / tiles_x) * SPLAT_TILE + (sub_a >> 2) * SUB;
   if (x0 >= W || y0 >= H) {
-    if (lane == 0) unit_cost[tile * UNITS_PER_TILE + unit] = 0u;
+    if (lane == 0) unit_cost[tile * UNITS_PER_TILE + unit] = blk_top[tile * UNITS_PER_TILE + unit] = 0u;
     return;
   }
   const int px = x0 + SUB * half + (p16 & 3), py = y0 + (p16 >> 2);
@@ -166,17 +166,13 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
   uint2 range = ranges[tile];
   range.x = min(range.x, capacity);   // only bites when the capacity hint was too small
   range.y = min(range.y, capacity);
-  const uint32_t len = range.y - range.x;
-  const uint32_t umask = 3u << sub_a;                           // the block's two mask bits
+  // the block's list (see block_list_kernel) and, indexed like it, what the backward reads
+  const size_t ubase = (size_t)UNITS_PER_TILE * range.x + (size_t)unit * (range.y - range.x);
+  const uint32_t len = min(blk_len[tile * UNITS_PER_TILE + unit], range.y - range.x);
+  const uint2 *bl = blist + ubase;
+  uint32_t *bw = bwords + (ubase >> 5) + tile * UNITS_PER_TILE + unit;
+  uint32_t *bp = bpix + ubase;
   const uint32_t lt = (1u << lane) - 1u;
-  // what the backward reads (see the header comment); a step word of this tile's step k lives
-  // at (range.x >> 5) + tile + k, unique per (tile, step)
-  uint32_t *words_a = blend_bits + (size_t)sub_a * bits_stride + (range.x >> 5) + tile;
-  uint32_t *words_b = words_a + bits_stride;
-  uint16_t *pix_a = pix_mask + (size_t)sub_a * pix_stride + range.x;
-  uint16_t *pix_b = pix_a + pix_stride;
-  const uint32_t *plist = point_list + range.x;
-  const uint16_t *smask = sub_mask + range.x;
 
   PixelState ps;
   ps.T = 1.0f;
@@ -187,29 +183,20 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
 
   const uint32_t nsteps = (len + 31) >> 5;
   uint32_t step = 0;
-  // Software pipeline of the walk: masks and surfel indices are fetched three steps ahead of
-  // their use, the records and cull boxes of a step's entries one step ahead (into registers):
-  // a record's address comes from an index loaded two steps earlier, so every L2 latency sits
-  // under the tests of the steps in between and under the evaluation phase.
-  uint32_t cmask = 0u, cid = 0u, nmask = 0u, nid = 0u, n2mask = 0u, n2id = 0u;
-  if (lane < len) {
-    cmask = smask[lane];
-    cid = plist[lane];
-  }
-  if (32 + lane < len) {
-    nmask = smask[32 + lane];
-    nid = plist[32 + lane];
-  }
-  if (64 + lane < len) {
-    n2mask = smask[64 + lane];
-    n2id = plist[64 + lane];
-  }
+  // Software pipeline of the walk: the list entries (surfel index, list position) are fetched
+  // three steps ahead of their use, the records and cull boxes of a step's entries one step
+  // ahead (into registers): a record's address comes from an index loaded two steps earlier,
+  // so every L2 latency sits under the tests of the steps in between and under the evaluation.
+  uint2 cent = make_uint2(0u, 0u), nent_r = cent, n2ent = cent;
+  if (lane < len) cent = bl[lane];
+  if (32 + lane < len) nent_r = bl[32 + lane];
+  if (64 + lane < len) n2ent = bl[64 + lane];
   float4 ra, rb, rc, rd, rcb;
   ra = rb = rc = rd = rcb = make_float4(0.f, 0.f, 0.f, 0.f);
-  if ((cmask & umask) != 0u) {
+  if (lane < len) {
     // (id < P only fails on the garbage a too-small capacity hint leaves behind; that frame is
     // re-run with the exact size)
-    const uint32_t id = min(cid, P - 1u);
+    const uint32_t id = min(cent.x, P - 1u);
     const float4 *r = rec + 4 * (size_t)id;
     ra = __ldg(r); rb = __ldg(r + 1); rc = __ldg(r + 2); rd = __ldg(r + 3);
     rcb = __ldg(cull + id);
@@ -217,71 +204,63 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
   __syncwarp();
 
   while (step < nsteps && !__all_sync(full, ps.done)) {
-    // ---- gather: stage the entries that can touch the block, queue the candidate pairs ----
+    // ---- gather: stage the step's entries, queue the candidate pairs ----
     int nent = 0, gsteps = 0;
     uint32_t pending = 0;
     const uint32_t step0 = step;
     while (step < nsteps && pending < GATHER_PAIRS && nent + 32 <= ENT_CAP && gsteps < STEP_CAP) {
-      const bool hit = (cmask & umask) != 0u;
-      const uint32_t vote = __ballot_sync(full, hit);
+      const bool hit = (step << 5) + lane < len;
+      const int ns = (int)min(32u, len - (step << 5));       // the hits are the low lanes
       const float4 a = ra, b = rb, c = rc, d = rd;
       float4 cb = rcb;
+      const uint32_t pos = cent.y;
       // advance the pipeline: this step's prefetched registers are consumed below
-      cmask = nmask;
-      cid = nid;
-      nmask = n2mask;
-      nid = n2id;
+      cent = nent_r;
+      nent_r = n2ent;
       {
         const uint32_t q = ((step + 3) << 5) + lane;
-        n2mask = 0u;
-        if (q < len) {
-          n2mask = smask[q];
-          n2id = plist[q];
-        }
+        if (q < len) n2ent = bl[q];
       }
-      if ((cmask & umask) != 0u) {
-        const uint32_t id = min(cid, P - 1u);
+      if (((step + 1) << 5) + lane < len) {
+        const uint32_t id = min(cent.x, P - 1u);
         const float4 *r = rec + 4 * (size_t)id;
         ra = __ldg(r); rb = __ldg(r + 1); rc = __ldg(r + 2); rd = __ldg(r + 3);
         rcb = __ldg(cull + id);
       }
-      if (lane == 0) st.word_a[gsteps] = st.word_b[gsteps] = 0u;
-      if (vote) {
-        if (hit) {
-          const int slot = nent + __popc(vote & lt);
-          st.rec[slot][0] = a; st.rec[slot][1] = b; st.rec[slot][2] = c; st.rec[slot][3] = d;
-          // x is periodic: bring the box into the first period in which it can reach this block
-          // (the smallest shift that puts its right edge at or beyond the block's left edge),
-          // once per entry; a pixel of the block is then inside the box in that period or - a
-          // box almost a period wide - beyond the left edge of the next one.  A box without
-          // culling information (+-inf, or not meaningful at all) accepts every pixel.
-          if (!cull_on) cb = make_float4(-3.0e38f, 3.0e38f, -3.0e38f, 3.0e38f);
-          if (cb.x > -3.0e38f && cb.y < 3.0e38f) {
-            const float k = ceilf(((float)x0 - cb.y) * inv_period) * period;
-            cb.x += k;
-            cb.y += k;
-          }
-          // the quarter-pixel margin of the box (dssr_preprocess.cu:cull_box) dwarfs the
-          // rounding of the shift (< 1e-3 pixel on images up to 8192 wide)
-          st.cull[slot] = cb;
-          st.cut[slot] = rho_cutoff(d.x);
-          st.ent_pos[slot] = (step << 5) + lane + 1u;      // the reference's `contributor`
-          st.ent_mask[slot] = 0u;
+      if (lane == 0) st.word[gsteps] = 0u;
+      if (hit) {
+        const int slot = nent + lane;
+        st.rec[slot][0] = a; st.rec[slot][1] = b; st.rec[slot][2] = c; st.rec[slot][3] = d;
+        // x is periodic: bring the box into the first period in which it can reach this block
+        // (the smallest shift that puts its right edge at or beyond the block's left edge),
+        // once per entry; a pixel of the block is then inside the box in that period or - a
+        // box almost a period wide - beyond the left edge of the next one.  A box without
+        // culling information (+-inf, or not meaningful at all) accepts every pixel.
+        if (!cull_on) cb = make_float4(-3.0e38f, 3.0e38f, -3.0e38f, 3.0e38f);
+        if (cb.x > -3.0e38f && cb.y < 3.0e38f) {
+          const float k = ceilf(((float)x0 - cb.y) * inv_period) * period;
+          cb.x += k;
+          cb.y += k;
         }
-        __syncwarp();
-        const int ns = __popc(vote);
-        for (int k = 0; k < ns; k++) {
-          const int slot = nent + k;
-          const float4 cb = st.cull[slot];
-          // (written so that a NaN in the box answers "candidate")
-          const bool cand = !ps.done && !(pyf < cb.z) && !(pyf > cb.w) &&
-                            ((!(pxf < cb.x) && !(pxf > cb.y)) || !(pxf < cb.x + period));
-          const uint32_t cv = __ballot_sync(full, cand);
-          if (cand) st.queue[pending + __popc(cv & lt)] = (uint16_t)((slot << 5) | lane);
-          pending += __popc(cv);
-        }
-        nent += ns;
+        // the quarter-pixel margin of the box (dssr_preprocess.cu:cull_box) dwarfs the
+        // rounding of the shift (< 1e-3 pixel on images up to 8192 wide)
+        st.cull[slot] = cb;
+        st.cut[slot] = rho_cutoff(d.x);
+        st.ent_pos[slot] = pos + 1u;                       // the reference's `contributor`
+        st.ent_mask[slot] = 0u;
       }
+      __syncwarp();
+      for (int k = 0; k < ns; k++) {
+        const int slot = nent + k;
+        const float4 cb = st.cull[slot];
+        // (written so that a NaN in the box answers "candidate")
+        const bool cand = !ps.done && !(pyf < cb.z) && !(pyf > cb.w) &&
+                          ((!(pxf < cb.x) && !(pxf > cb.y)) || !(pxf < cb.x + period));
+        const uint32_t cv = __ballot_sync(full, cand);
+        if (cand) st.queue[pending + __popc(cv & lt)] = (uint16_t)((slot << 5) | lane);
+        pending += __popc(cv);
+      }
+      nent += ns;
       step++;
       gsteps++;
     }
@@ -357,27 +336,17 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
     }
 
     // ---- write down what was blended in this phase's steps ----
+    // (entry e of the phase is entry (step0 << 5) + e of the block's list: only a list's last
+    // step can be short)
     for (int e = lane; e < nent; e += 32) {
       const uint32_t m = st.ent_mask[e];
       if (m) {
-        const uint32_t q = st.ent_pos[e] - 1u;
-        const uint32_t bit = 1u << (q & 31u);
-        const uint32_t k = (q >> 5) - step0;
-        if (m & 0xffffu) {
-          pix_a[q] = (uint16_t)(m & 0xffffu);
-          atomicOr(&st.word_a[k], bit);
-        }
-        if (m >> 16) {
-          pix_b[q] = (uint16_t)(m >> 16);
-          atomicOr(&st.word_b[k], bit);
-        }
+        bp[(step0 << 5) + e] = m;
+        atomicOr(&st.word[e >> 5], 1u << (e & 31));
       }
     }
     __syncwarp();
-    if (lane < gsteps) {
-      words_a[step0 + lane] = st.word_a[lane];
-      words_b[step0 + lane] = st.word_b[lane];
-    }
+    if (lane < gsteps) bw[step0 + lane] = st.word[lane];
     __syncwarp();
     STAGE_CLOCK(c_write)
   }
@@ -395,7 +364,10 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
   // what the backward will have to do for this block: the number of blended (pixel, entry)
   // pairs (its warps are numbered by decreasing cost, see bwd_order_kernel)
   npairs = __reduce_add_sync(full, npairs);
-  if (lane == 0) unit_cost[tile * UNITS_PER_TILE + unit] = npairs;
+  if (lane == 0) {
+    unit_cost[tile * UNITS_PER_TILE + unit] = npairs;
+    blk_top[tile * UNITS_PER_TILE + unit] = step;     // steps of the block's list that were walked
+  }
   if (inside) {
     const size_t HW = (size_t)W * H;
     const size_t pix = (size_t)py * W + px;
@@ -487,7 +459,7 @@ void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageVie
     cudaFuncSetAttribute(render_forward_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                          cudaSharedmemCarveoutMaxShared);
   render_forward_kernel<<<im.tiles * UNITS_PER_TILE, 32, 0, LS(s)>>>(
-      im.ranges, order, b.point_list, b.sub_mask, g.rec, g.cull, p.projmatrix, p.W, p.H, im.tiles_x,
-      capacity, (uint32_t)p.P, im.final_T, im.n_contrib, p.out_maps, im.sub_cost, b.blend_bits,
-      b.bits_stride, b.pix_mask, b.pix_stride);
+      im.ranges, order, b.blist, im.blk_len, g.rec, g.cull, p.projmatrix, p.W, p.H, im.tiles_x,
+      capacity, (uint32_t)p.P, im.final_T, im.n_contrib, p.out_maps, im.sub_cost, im.blk_top,
+      b.bwords, b.bpix);
 }

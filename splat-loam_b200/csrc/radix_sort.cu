@@ -718,6 +718,84 @@ tile_sort_kernel(unsigned long long *words, unsigned long long *alt,
   TRACE(11)
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Block lists.  The compositing kernels work on 8x4-pixel blocks, 8 per tile; a block is
+// touched by a few per cent of its tile's entries (the sub-tile masks say which).  One CTA per
+// tile splits the tile's sorted list into the 8 lists of its blocks, in list order, so that a
+// block's warp reads only what concerns it instead of scanning the whole tile list:
+//   blist[8 * ranges[t].x + u * len(t) + c] = (surfel index, position in the tile's list)
+// for the c-th entry whose mask has one of the block's two bits (2u, 2u + 1).
+constexpr int BL_THREADS = 1024;
+constexpr int BL_WARPS = BL_THREADS / 32;
+
+__global__ void __launch_bounds__(BL_THREADS)
+block_list_kernel(const uint2 *__restrict__ ranges, uint32_t capacity,
+                  const uint32_t *__restrict__ point_list, const uint16_t *__restrict__ sub_mask,
+                  uint2 *__restrict__ blist, uint32_t *__restrict__ blk_len) {
+  __shared__ uint32_t s_cnt[BL_WARPS][SPLAT_BLOCKS_PER_TILE];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const uint32_t tile = blockIdx.x;
+  uint2 rg = ranges[tile];
+  rg.x = min(rg.x, capacity);          // only bites when the capacity hint was too small
+  rg.y = min(rg.y, capacity);
+  const uint32_t n = rg.y - rg.x;
+  if (n == 0) {
+    if (tid < SPLAT_BLOCKS_PER_TILE) blk_len[tile * SPLAT_BLOCKS_PER_TILE + tid] = 0u;
+    return;
+  }
+  const uint16_t *sm = sub_mask + rg.x;
+  const uint32_t *pl = point_list + rg.x;
+  const uint32_t chunk = ((n + BL_WARPS - 1) / BL_WARPS + 31u) & ~31u;   // entries per warp
+  const uint32_t w0 = min(n, (uint32_t)wid * chunk), w1 = min(n, w0 + chunk);
+  const uint32_t lt = (1u << lane) - 1u;
+  // pass 1: how many entries of this warp's part go to each block
+  uint32_t cnt[SPLAT_BLOCKS_PER_TILE];
+#pragma unroll
+  for (int u = 0; u < SPLAT_BLOCKS_PER_TILE; u++) cnt[u] = 0u;
+  for (uint32_t i0 = w0; i0 < w1; i0 += 32) {
+    const uint32_t i = i0 + lane;
+    const uint32_t m = i < w1 ? (uint32_t)sm[i] : 0u;
+#pragma unroll
+    for (int u = 0; u < SPLAT_BLOCKS_PER_TILE; u++)
+      cnt[u] += __popc(__ballot_sync(0xffffffffu, ((m >> (2 * u)) & 3u) != 0u));
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int u = 0; u < SPLAT_BLOCKS_PER_TILE; u++) s_cnt[wid][u] = cnt[u];
+  }
+  __syncthreads();
+  // exclusive prefix over the warps, per block (one thread per block)
+  if (tid < SPLAT_BLOCKS_PER_TILE) {
+    uint32_t run = 0;
+    for (int w = 0; w < BL_WARPS; w++) {
+      const uint32_t c = s_cnt[w][tid];
+      s_cnt[w][tid] = run;
+      run += c;
+    }
+    blk_len[tile * SPLAT_BLOCKS_PER_TILE + tid] = run;
+  }
+  __syncthreads();
+  // pass 2: write
+  uint32_t off[SPLAT_BLOCKS_PER_TILE];
+#pragma unroll
+  for (int u = 0; u < SPLAT_BLOCKS_PER_TILE; u++) off[u] = s_cnt[wid][u];
+  uint2 *base = blist + (size_t)SPLAT_BLOCKS_PER_TILE * rg.x;
+  for (uint32_t i0 = w0; i0 < w1; i0 += 32) {
+    const uint32_t i = i0 + lane;
+    const bool in = i < w1;
+    const uint32_t m = in ? (uint32_t)sm[i] : 0u;
+    const uint32_t id = in ? pl[i] : 0u;
+#pragma unroll
+    for (int u = 0; u < SPLAT_BLOCKS_PER_TILE; u++) {
+      const bool hit = ((m >> (2 * u)) & 3u) != 0u;
+      const uint32_t vote = __ballot_sync(0xffffffffu, hit);
+      if (hit) base[(size_t)u * n + off[u] + __popc(vote & lt)] = make_uint2(id, i);
+      off[u] += __popc(vote);
+    }
+  }
+}
+
 }  // namespace
 
 #ifdef SORT_TRACE
@@ -868,6 +946,8 @@ void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, con
     tile_sort_kernel<<<im.tiles, TS_THREADS, TS_SMEM, LS(s)>>>(
         b.words_b, b.words_a, im.ranges, im.tile_order, capacity, b.keys, b.point_list, mp,
         (uint32_t)p.P, sp.idx_bits);
+    block_list_kernel<<<im.tiles, BL_THREADS, 0, LS(s)>>>(im.ranges, capacity, b.point_list,
+                                                       b.sub_mask, b.blist, im.blk_len);
     return;
   }
   launch_sort_passes(b.words_a, b.words_b, b.keys, b.point_list, &g.hdr->num_rendered,
@@ -882,4 +962,6 @@ void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, con
   }
   if (single < 0 && im.tiles <= SPLAT_MAX_ORDERED_TILES)   // beyond that: identity order
     tile_order_kernel<<<(im.tiles + 127) / 128, 128, 0, LS(s)>>>(im.ranges, im.tiles, im.tile_order);
+  block_list_kernel<<<im.tiles, BL_THREADS, 0, LS(s)>>>(im.ranges, capacity, b.point_list,
+                                                     b.sub_mask, b.blist, im.blk_len);
 }
