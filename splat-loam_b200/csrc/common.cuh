@@ -123,7 +123,9 @@ struct BinHeader {
   uint32_t magic;
   uint32_t capacity;
   uint32_t keep_unsorted;
-  uint32_t pad;
+  // 1: the sort did not materialise point_list_keys (tile-first path); dssr_debug_state
+  // rebuilds them from point_list, ranges and the surfels' depths (launch_rebuild_keys)
+  uint32_t keys_deferred;
   // byte offset (from the aligned buffer start) of sub_mask: the backward only knows
   // num_rendered, not the capacity the forward laid the buffer out with
   unsigned long long off_sub_mask;
@@ -312,6 +314,8 @@ void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, con
 // 16-bit sub-tile mask (into the `keys` array, which nothing else uses before the sort's last
 // kernel), and the partition pass packs it into the word's top 16 bits.
 bool sort_tile_first(const SortPlan &sp, int tiles);
+void launch_rebuild_keys(const ImageView &im, const GeomView &g, const BinView &b, uint32_t P,
+                         uint32_t capacity, cudaStream_t s);
 void launch_digit_scan(const uint32_t *hist, uint32_t *digit_base, int npass, uint2 *ranges,
                        uint32_t *tile_order, int tiles, int tile_pass_single, int nrepl,
                        cudaStream_t s);

@@ -411,8 +411,9 @@ int dssr_debug_state(const char *geom_buffer, const char *binning_buffer,
   SortPlan sp(P, iv.tiles);
   BinView bv;
   memset(&bv, 0, sizeof bv);
+  BinHeader bh;
+  memset(&bh, 0, sizeof bh);
   if (binning_buffer) {
-    BinHeader bh;
     CUDA_TRY(cudaMemcpy(&bh, align_ptr(binning_buffer), sizeof bh, cudaMemcpyDeviceToHost));
     if (bh.magic != 0x42494e31u) return fail("dssr_debug_state: not a binning buffer");
     bv = make_bin_view(binning_buffer, bh.capacity, bh.keep_unsorted, sp, iv.tiles);
@@ -429,7 +430,13 @@ int dssr_debug_state(const char *geom_buffer, const char *binning_buffer,
     if (n == "transMat") { *ptr = scratch; *count = 12 * (size_t)P; }
     else { *ptr = scratch + 12 * (size_t)P; *count = 4 * (size_t)P; }
   }
-  else if (n == "keys") { *ptr = bv.keys; *count = R; }
+  else if (n == "keys") {
+    if (binning_buffer && bh.keys_deferred) {   // not materialised by the tile-first sort
+      launch_rebuild_keys(iv, gv, bv, (uint32_t)P, bh.capacity, st);
+      CUDA_TRY(cudaStreamSynchronize(st));
+    }
+    *ptr = bv.keys; *count = R;
+  }
   else if (n == "point_list") { *ptr = bv.point_list; *count = R; }
   else if (n == "keys_unsorted") {
     if (!bv.keys_unsorted) return fail("dssr_debug_state: forward ran without debug bit1");

@@ -505,8 +505,9 @@ constexpr int TS_CAP = TS_THREADS * TS_ITEMS;
 constexpr size_t TS_SMEM = (size_t)TS_CAP * 8 + (size_t)TS_WARPS * TS_BINS * 4 +
                            (size_t)TS_WARPS * TS_BINS * 2 + 3 * TS_BINS * 4;
 
-// counts -> offsets: cnt[w][d] becomes the number of words with digit d in warps before w,
-// s_base[d] the number of words with a smaller digit.  1024 threads: (digit, half of the warps).
+// counts -> offsets: cnt[w][d] becomes the position of warp w's first word with digit d
+// (words with a smaller digit + words with digit d in the warps before w).  1024 threads:
+// (digit, half of the warps).
 template <typename CT>
 __device__ __forceinline__ void ts_scan(CT *cnt, uint32_t *s_half, uint32_t *s_base,
                                         uint32_t *s_warp) {
@@ -524,8 +525,6 @@ __device__ __forceinline__ void ts_scan(CT *cnt, uint32_t *s_half, uint32_t *s_b
   s_half[h * TS_BINS + d] = run;
   __syncthreads();
   const uint32_t add = h ? s_half[d] : 0u;
-#pragma unroll
-  for (int j = 0; j < 16; j++) cnt[(16 * h + j) * TS_BINS + d] = (CT)(c[j] + add);
   uint32_t tot = 0, inc = 0;
   if (tid < TS_BINS) {
     tot = s_half[tid] + s_half[TS_BINS + tid];
@@ -544,13 +543,18 @@ __device__ __forceinline__ void ts_scan(CT *cnt, uint32_t *s_half, uint32_t *s_b
     s_base[tid] = before + inc - tot;
   }
   __syncthreads();
+  // cnt[w][d] = words with a smaller digit + words with digit d in the warps before w
+  const uint32_t base = s_base[d] + add;
+#pragma unroll
+  for (int j = 0; j < 16; j++) cnt[(16 * h + j) * TS_BINS + d] = (CT)(c[j] + base);
+  __syncthreads();
 }
 
 __global__ void __launch_bounds__(TS_THREADS, 1)
 tile_sort_kernel(unsigned long long *words, unsigned long long *alt,
                  const uint2 *__restrict__ ranges, const uint32_t *__restrict__ tile_order,
-                 uint32_t capacity, unsigned long long *__restrict__ keys_out,
-                 uint32_t *__restrict__ plist_out, MaskParams mp, uint32_t P, int idx_bits) {
+                 uint32_t capacity, uint32_t *__restrict__ plist_out, int idx_bits,
+                 uint2 *__restrict__ blist, uint32_t *__restrict__ blk_len) {
   extern __shared__ unsigned long long ts_smem[];
   unsigned long long *s_buf = ts_smem;                                   // [TS_CAP]
   uint32_t *tbl = reinterpret_cast<uint32_t *>(s_buf + TS_CAP);          // [TS_WARPS][TS_BINS]
@@ -565,7 +569,10 @@ tile_sort_kernel(unsigned long long *words, unsigned long long *alt,
   rg.x = min(rg.x, capacity);          // only bites when the capacity hint was too small
   rg.y = min(rg.y, capacity);
   const uint32_t n = rg.y - rg.x;
-  if (n == 0) return;
+  if (n == 0) {
+    if (tid < SPLAT_BLOCKS_PER_TILE) blk_len[tile * SPLAT_BLOCKS_PER_TILE + tid] = 0u;
+    return;
+  }
 #ifdef SORT_TRACE
   const uint32_t bid = blockIdx.x;
   if (tid == 0 && bid < 1024) g_trace[bid][12] = n;
@@ -636,14 +643,20 @@ tile_sort_kernel(unsigned long long *words, unsigned long long *alt,
 #ifdef SORT_TRACE
       if (tid == 0 && bid < 1024) g_trace[bid][3 + 3 * pass] = gtime();
 #endif
+      // (positions first, stores after: the compiler must assume the tables and the word
+      // buffer alias and would otherwise order every table load behind the previous store)
 #pragma unroll
       for (int r = 0; r < TS_ITEMS; r++) {
         if (r < items) {
           const uint32_t i = wbase + r * 32 + lane;
-          if (i < n) {
-            const uint32_t digit = (uint32_t)(key[r] >> shift) & (TS_BINS - 1);
-            s_buf[s_base[digit] + my_cnt[digit] + rank[r]] = key[r];
-          }
+          if (i < n) rank[r] += my_cnt[(uint32_t)(key[r] >> shift) & (TS_BINS - 1)];
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < TS_ITEMS; r++) {
+        if (r < items) {
+          const uint32_t i = wbase + r * 32 + lane;
+          if (i < n) s_buf[rank[r]] = key[r];
         }
       }
       __syncthreads();
@@ -693,7 +706,7 @@ tile_sort_kernel(unsigned long long *words, unsigned long long *alt,
           my_cnt[digit] = old + __popc(peers);
         }
         old = __shfl_sync(0xffffffffu, old, leader);
-        if (valid) b[s_base[digit] + old + __popc(peers & lt)] = k;
+        if (valid) b[old + __popc(peers & lt)] = k;
         __syncwarp();
       }
       __threadfence_block();
@@ -705,15 +718,63 @@ tile_sort_kernel(unsigned long long *words, unsigned long long *alt,
     fin = a;
   }
 
-  // ---- write-out: the reference's arrays; the sub-tile mask rides in the word's top bits ----
+  // ---- write-out: the reference's point_list, and the 8 block lists of the tile (see
+  // block_list_kernel below; the sub-tile mask rides in the word's top bits) ----
+  // (point_list_keys is not materialised on this path: every key is (tile << 32) | bits of
+  // depths[point_list[i]], which rebuild_keys_kernel writes out when dssr_debug_state asks)
   const unsigned long long idx_mask = (1ull << idx_bits) - 1ull;
-  for (uint32_t j = tid; j < n; j += TS_THREADS) {
-    const unsigned long long k = fin[j];
-    const uint32_t pos = rg.x + j;
-    const uint32_t d27 = (uint32_t)(k >> idx_bits) & ((1u << SPLAT_DEPTH_BITS) - 1u);
-    keys_out[pos] = ((unsigned long long)tile << 32) | (unsigned long long)(d27 + SPLAT_DEPTH_BASE);
-    plist_out[pos] = (uint32_t)(k & idx_mask);
-    if (mp.sub_mask) mp.sub_mask[pos] = (uint16_t)(k >> 48);
+  for (uint32_t j = tid; j < n; j += TS_THREADS) plist_out[rg.x + j] = (uint32_t)(fin[j] & idx_mask);
+  TRACE(13)
+  // Every thread takes a run of consecutive entries and counts, per block, the entries of its
+  // run that touch it; a scan over the threads turns the counts into each run's first position
+  // in the 8 lists.  (A version with one warp ballot per block and 32 entries spent 8 us of
+  // the CTA's 25 in this phase: VOTE and POPC issue far below the rate of plain arithmetic.)
+  uint32_t(*s_bcnt)[SPLAT_BLOCKS_PER_TILE] =
+      reinterpret_cast<uint32_t(*)[SPLAT_BLOCKS_PER_TILE]>(s_half);     // [TS_WARPS][8], scan scratch
+  const uint32_t ipt = (n + TS_THREADS - 1) / TS_THREADS;
+  const uint32_t e0 = min(n, (uint32_t)tid * ipt), e1 = min(n, e0 + ipt);
+  uint32_t bcnt[SPLAT_BLOCKS_PER_TILE], binc[SPLAT_BLOCKS_PER_TILE];
+#pragma unroll
+  for (int u = 0; u < SPLAT_BLOCKS_PER_TILE; u++) bcnt[u] = 0u;
+  for (uint32_t i = e0; i < e1; i++) {
+    const uint32_t m = (uint32_t)(fin[i] >> 48);
+#pragma unroll
+    for (int u = 0; u < SPLAT_BLOCKS_PER_TILE; u++) bcnt[u] += ((m >> (2 * u)) & 3u) != 0u;
+  }
+#pragma unroll
+  for (int u = 0; u < SPLAT_BLOCKS_PER_TILE; u++) {
+    uint32_t inc = bcnt[u];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    binc[u] = inc;
+    if (lane == 31) s_bcnt[wid][u] = inc;
+  }
+  TRACE(14)
+  __syncthreads();
+  if (tid < SPLAT_BLOCKS_PER_TILE) {
+    uint32_t run = 0;
+    for (int w = 0; w < TS_WARPS; w++) {
+      const uint32_t c = s_bcnt[w][tid];
+      s_bcnt[w][tid] = run;
+      run += c;
+    }
+    blk_len[tile * SPLAT_BLOCKS_PER_TILE + tid] = run;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int u = 0; u < SPLAT_BLOCKS_PER_TILE; u++) bcnt[u] = s_bcnt[wid][u] + binc[u] - bcnt[u];
+  uint2 *bbase = blist + (size_t)SPLAT_BLOCKS_PER_TILE * rg.x;
+  TRACE(15)
+  for (uint32_t i = e0; i < e1; i++) {
+    const unsigned long long k = fin[i];
+    const uint32_t m = (uint32_t)(k >> 48);
+    const uint2 e = make_uint2((uint32_t)(k & idx_mask), i);
+#pragma unroll
+    for (int u = 0; u < SPLAT_BLOCKS_PER_TILE; u++)
+      if (((m >> (2 * u)) & 3u) != 0u) bbase[(size_t)u * n + bcnt[u]++] = e;
   }
   TRACE(11)
 }
@@ -905,6 +966,27 @@ unsigned long long *launch_sort_passes(unsigned long long *a, unsigned long long
   return src;
 }
 
+// point_list_keys for dssr_debug_state when the sort did not write them: key i of tile t is
+// (t << 32) | bits(depth of surfel point_list[i]) - the word the reference sorts.
+__global__ void rebuild_keys_kernel(const uint2 *__restrict__ ranges, uint32_t capacity,
+                                    const uint32_t *__restrict__ point_list,
+                                    const float *__restrict__ depths, uint32_t P,
+                                    unsigned long long *__restrict__ keys) {
+  const uint32_t tile = blockIdx.x;
+  uint2 rg = ranges[tile];
+  rg.x = min(rg.x, capacity);
+  rg.y = min(rg.y, capacity);
+  for (uint32_t i = rg.x + threadIdx.x; i < rg.y; i += blockDim.x)
+    keys[i] = ((unsigned long long)tile << 32) |
+              (unsigned long long)__float_as_uint(depths[min(point_list[i], P - 1u)]);
+}
+
+void launch_rebuild_keys(const ImageView &im, const GeomView &g, const BinView &b, uint32_t P,
+                         uint32_t capacity, cudaStream_t s) {
+  rebuild_keys_kernel<<<im.tiles, 256, 0, LS(s)>>>(im.ranges, capacity, b.point_list,
+                                                  g.depths, P, b.keys);
+}
+
 // Tile-first needs the tile id in one digit (<= 1024 tiles) and 16 free bits above
 // [depth27 | idx] for the sub-tile mask (<= 2 M surfels); SPLAT_B200_SORT=global keeps the four
 // global passes (developer A/B switch).
@@ -944,10 +1026,8 @@ void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, con
     else PART_PASS(8);
 #undef PART_PASS
     tile_sort_kernel<<<im.tiles, TS_THREADS, TS_SMEM, LS(s)>>>(
-        b.words_b, b.words_a, im.ranges, im.tile_order, capacity, b.keys, b.point_list, mp,
-        (uint32_t)p.P, sp.idx_bits);
-    block_list_kernel<<<im.tiles, BL_THREADS, 0, LS(s)>>>(im.ranges, capacity, b.point_list,
-                                                       b.sub_mask, b.blist, im.blk_len);
+        b.words_b, b.words_a, im.ranges, im.tile_order, capacity, b.point_list, sp.idx_bits,
+        b.blist, im.blk_len);
     return;
   }
   launch_sort_passes(b.words_a, b.words_b, b.keys, b.point_list, &g.hdr->num_rendered,

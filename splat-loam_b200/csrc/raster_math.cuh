@@ -165,18 +165,30 @@ __device__ __forceinline__ bool cull_overlap(float4 cb, float x0, float x1, floa
 
 // Which of the 16 4x4-pixel sub-tiles of the 16x16 tile at (tx0, ty0) can the surfel's cull
 // box touch?  bit (sy*4 + sx).  Same NaN-means-yes convention as cull_overlap.
-__device__ __forceinline__ uint32_t subtile_mask(float4 cb, float tx0, float ty0,
-                                                 float inv_period) {
-  uint32_t rm = 0, cm = 0;
+// (rows and columns separately: a caller that walks a row of tiles computes the rows once)
+__device__ __forceinline__ uint32_t subtile_rows(float4 cb, float ty0) {
+  uint32_t rm = 0;
 #pragma unroll
   for (int i = 0; i < 4; i++) {
-    const float y0 = ty0 + 4.0f * i, x0 = tx0 + 4.0f * i;
+    const float y0 = ty0 + 4.0f * i;
     if (!(cb.z > y0 + 3.0f) && !(cb.w < y0)) rm |= 1u << i;
+  }
+  return rm;
+}
+__device__ __forceinline__ uint32_t subtile_cols(float4 cb, float tx0, float inv_period) {
+  uint32_t cm = 0;
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const float x0 = tx0 + 4.0f * i;
     if (!(floorf((x0 + 3.0f - cb.x) * inv_period) < ceilf((x0 - cb.y) * inv_period))) cm |= 1u << i;
   }
-  uint32_t m = 0;
-#pragma unroll
-  for (int r = 0; r < 4; r++)
-    if (rm & (1u << r)) m |= cm << (4 * r);
-  return m;
+  return cm;
+}
+__device__ __forceinline__ uint32_t subtile_combine(uint32_t rm, uint32_t cm) {
+  return (cm * 0x1111u) & (((rm & 1u) * 0xfu) | ((rm & 2u) * 0x78u) | ((rm & 4u) * 0x3c0u) |
+                           ((rm & 8u) * 0x1e00u));
+}
+__device__ __forceinline__ uint32_t subtile_mask(float4 cb, float tx0, float ty0,
+                                                 float inv_period) {
+  return subtile_combine(subtile_rows(cb, ty0), subtile_cols(cb, tx0, inv_period));
 }

@@ -26,3 +26,6 @@ print("second wave starts at %.1f us" % ((np.sort(t[:, 0])[min(148, len(t) - 1)]
 d = np.diff(t[:, :12], axis=1) / 1000.0
 print("phase medians (us): " + ", ".join(f"{names[j]} {np.median(d[:, j]):.2f}" for j in range(11)))
 print("per CTA total median %.1f us, max %.1f us" % (np.median(t[:, 11] - t[:, 0]) / 1000, (t[:, 11] - t[:, 0]).max() / 1000))
+w = t[:, [10, 13, 14, 15, 11]]
+dw = np.diff(w, axis=1) / 1000.0
+print("write-out parts (median us): point_list %.2f, count+warp scan %.2f, block scan %.2f, list stores %.2f" % tuple(np.median(dw, axis=0)))
