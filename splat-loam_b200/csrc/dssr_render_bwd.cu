@@ -117,8 +117,6 @@ struct __align__(16) WarpStage {
   float4 pout[32];                  // P2 -> P3: T, dL_dalpha, dLd_depth, w of the batch's pairs
   uint32_t ent_id[ENT_CAP];         // surfel index
   uint32_t ent_pos[ENT_CAP];        // position in the tile's list (the reference's `contributor`)
-  uint32_t ent_mask[ENT_CAP];       // pixels that blended it (bit = lane of the pixel)
-  uint32_t ent_prefix[ENT_CAP + 1]; // exclusive prefix of the pair counts
   float ray[10][32];                // per pixel: X Y Z ax ay ex ey ez pxf pyf
   float gN[3][32];                  // per pixel: dL_dout of the normal channels
   float pa[32], pd[32];             // P1 -> P2: alpha, depth of the batch's pairs
@@ -269,22 +267,28 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
     if (vote) {                                                                                  \
       const bool any = (vote >> lane) & 1u;                                                      \
       const int ns = __popc(vote);                                                               \
+      const int slot = nent + __popc(vote >> lane) - 1; /* later entries first */                \
       if (any) {                                                                                 \
-        const int slot = nent + __popc(vote >> lane) - 1; /* later entries first */              \
         st.ent_id[slot] = id;                                                                    \
         st.ent_pos[slot] = pos;                                                                  \
-        st.ent_mask[slot] = mask;                                                                \
         st.rec[slot][0] = a; st.rec[slot][1] = b; st.rec[slot][2] = c; st.rec[slot][3] = d;      \
       }                                                                                          \
-      __syncwarp();                                                                              \
-      /* lay the entries' pairs end to end: every pixel's lane appends itself */                 \
-      for (int k = 0; k < ns; k++) {                                                             \
-        const int slot = nent + k;                                                               \
-        const uint32_t m = st.ent_mask[slot];                                                    \
-        if (lane == 0) st.ent_prefix[slot] = pending;                                            \
-        if ((m >> lane) & 1u) st.queue[pending + __popc(m & lt)] = (uint16_t)((slot << 5) | lane); \
-        pending += __popc(m);                                                                    \
+      /* lay the entries' pairs end to end, in slot order: every entry's lane writes its own */  \
+      uint32_t m = any ? mask : 0u;                                                              \
+      uint32_t suf = __popc(m);                      /* pairs of this and the later lanes */     \
+      _Pragma("unroll") for (int o = 1; o < 32; o <<= 1) {                                       \
+        const uint32_t t = __shfl_down_sync(full, suf, o);                                       \
+        if (lane + o < 32) suf += t;                                                             \
       }                                                                                          \
+      uint32_t w = pending + suf - __popc(m);                                                    \
+      const uint32_t tag = (uint32_t)slot << 5;                                                  \
+      for (int it = (int)__reduce_max_sync(full, (unsigned)__popc(m)); it > 0; it--) {           \
+        if (m) {                                                                                 \
+          st.queue[w++] = (uint16_t)(tag | (uint32_t)(__ffs(m) - 1));                            \
+          m &= m - 1u;                                                                           \
+        }                                                                                        \
+      }                                                                                          \
+      pending += __shfl_sync(full, suf, 0);                                                      \
       nent += ns;                                                                                \
     }                                                                                            \
     chunk--;                                                                                     \
@@ -305,7 +309,6 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
       if (chunk < 0) break;
       continue;
     }
-    if (lane == 0) st.ent_prefix[nent] = pending;
     __syncwarp();
     STAGE_CLOCK(c_gather)
 

@@ -102,7 +102,6 @@ __device__ __forceinline__ bool blend(PixelState &p, float alpha, float depth, f
 // everything a warp stages in shared memory (one warp per CTA)
 struct __align__(16) FwdStage {
   float4 rec[ENT_CAP][4];        // the staged entries' 64-byte records
-  uint2 cand[ENT_CAP];           // the entry's candidate pixels (bit = lane), where its pairs start
   uint32_t ent_pos[ENT_CAP];     // the reference's `contributor` (1-based list position)
   uint32_t ent_mask[ENT_CAP];    // pixels that blended the entry (bit = lane of the pixel)
   uint32_t word[STEP_CAP];       // the phase's step words
@@ -275,12 +274,16 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
         const uint32_t t = __shfl_up_sync(full, inc, o);
         if (lane >= o) inc += t;
       }
-      if (hit) st.cand[nent + lane] = make_uint2(cm, pending + inc - __popc(cm));
-      __syncwarp();
-#pragma unroll 4
-      for (int k = 0; k < ns; k++) {
-        const uint2 e = st.cand[nent + k];
-        if ((e.x >> lane) & 1u) st.queue[e.y + __popc(e.x & lt)] = (uint16_t)(((nent + k) << 5) | lane);
+      // the entry's lane writes the entry's pairs, pixel by pixel
+      {
+        uint32_t m = cm, w = pending + inc - __popc(cm);
+        const uint32_t tag = (uint32_t)(nent + lane) << 5;
+        for (int it = (int)__reduce_max_sync(full, (unsigned)__popc(cm)); it > 0; it--) {
+          if (m) {
+            st.queue[w++] = (uint16_t)(tag | (uint32_t)(__ffs(m) - 1));
+            m &= m - 1u;
+          }
+        }
       }
       pending += __shfl_sync(full, inc, 31);
       nent += ns;
