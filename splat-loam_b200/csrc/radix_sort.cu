@@ -271,7 +271,8 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
                       MaskParams mp, uint32_t P, const uint32_t *__restrict__ num_ptr,
                       uint32_t capacity, uint32_t *status, uint32_t *ticket,
                       const uint32_t *__restrict__ digit_base, int shift, int bits, int idx_bits,
-                      const uint16_t *__restrict__ mask_in) {
+                      const uint16_t *__restrict__ mask_in, const uint32_t *__restrict__ hist,
+                      uint2 *ranges, uint32_t *tile_order, int tiles) {
   extern __shared__ uint32_t smem[];
   const int bins = 1 << bits;
   uint16_t *s_cnt = reinterpret_cast<uint16_t *>(smem);            // [WARPS][bins]
@@ -286,6 +287,10 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
   uint16_t *s_mask = reinterpret_cast<uint16_t *>(
       reinterpret_cast<char *>(s_stage) +
       (SORT_THREADS * ITEMS * 8 > WARPS * bins * 4 ? SORT_THREADS * ITEMS * 8 : WARPS * bins * 4));
+  // partition mode: every CTA scans the tile histogram itself (digit_base of its digits, the
+  // tile ranges), which saves the digit-scan kernel in front of this one
+  uint32_t *s_dbase = reinterpret_cast<uint32_t *>(s_mask + SORT_THREADS * ITEMS);   // [bins]
+  uint32_t *s_len = s_dbase + bins;                                                  // [bins]
   __shared__ uint32_t s_bid;
   __shared__ uint32_t s_warp[WARPS];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -293,10 +298,56 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
   if (tid == 0) s_bid = atomicAdd(ticket, 1u);
   for (int i = tid; i < (WARPS * bins) / 2; i += SORT_THREADS) smem[i] = 0u;
   for (int i = tid; i < WARPS * bins; i += SORT_THREADS) s_tbl[i] = 0u;
+  if (!UNPACK) {
+    const int ipt = (bins + SORT_THREADS - 1) / SORT_THREADS;     // 1 or 2
+    const int d0 = tid * ipt;
+    uint32_t v0 = 0u, v1 = 0u;
+    if (d0 < bins) {
+#pragma unroll 8
+      for (int r = 0; r < HIST_REPL; r++) v0 += hist[(size_t)r * (SORT_MAX_PASSES * SORT_MAX_BINS) + d0];
+    }
+    if (ipt > 1 && d0 + 1 < bins) {
+#pragma unroll 8
+      for (int r = 0; r < HIST_REPL; r++) v1 += hist[(size_t)r * (SORT_MAX_PASSES * SORT_MAX_BINS) + d0 + 1];
+    }
+    uint32_t inc = v0 + v1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += n;
+    }
+    if (lane == 31) s_warp[wid] = inc;
+    __syncthreads();
+    uint32_t before = 0;
+    for (int w = 0; w < wid; w++) before += s_warp[w];
+    const uint32_t excl = before + inc - (v0 + v1);
+    if (d0 < bins) { s_dbase[d0] = excl; s_len[d0] = v0; }
+    if (ipt > 1 && d0 + 1 < bins) { s_dbase[d0 + 1] = excl + v0; s_len[d0 + 1] = v1; }
+  }
   __syncthreads();
   const uint32_t bid = s_bid;
+  // ranges[tile] = [start, end) ((0,0) for an empty tile: what the reference's memset +
+  // identifyTileRanges leaves) and the work order, tile_order[rank] = tile by decreasing list
+  // length - written by the first CTA when it is done with its words
+  auto write_ranges = [&]() {
+    for (int d = tid; d < tiles; d += SORT_THREADS) {
+      const uint32_t v = s_len[d], b0 = s_dbase[d];
+      ranges[d] = v ? make_uint2(b0, b0 + v) : make_uint2(0u, 0u);
+      if (tile_order) {
+        uint32_t rank = 0;
+        for (int o = 0; o < tiles; o++) {
+          const uint32_t l = s_len[o];
+          rank += (l > v) || (l == v && o < d);
+        }
+        tile_order[rank] = (uint32_t)d;
+      }
+    }
+  };
   const uint32_t start = bid * (SORT_THREADS * ITEMS);
-  if (start >= N) return;
+  if (start >= N) {
+    if (!UNPACK && bid == 0) write_ranges();
+    return;
+  }
   const uint32_t count = min((uint32_t)(SORT_THREADS * ITEMS), N - start);
   TRACE(0)
 
@@ -419,7 +470,7 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
       }
       st_volatile_u32(&my_status[d], FLAG_INCL | (excl + total));
     }
-    s_base[d] = digit_base[d] + excl - s_loc[d];
+    s_base[d] = (UNPACK ? digit_base[d] : s_dbase[d]) + excl - s_loc[d];
   }
   TRACE(5)
   __syncthreads();
@@ -433,6 +484,7 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
       const uint32_t pos = j + s_base[(uint32_t)(k >> shift) & mask];
       if (pos < capacity) keys_out[pos] = ((unsigned long long)s_mask[j] << 48) | (k & low);
     }
+    if (bid == 0) write_ranges();
     return;
   }
   const unsigned long long idx_mask = (1ull << idx_bits) - 1ull;
@@ -900,7 +952,9 @@ static void launch_one_pass(int last /* 1: unpacking last pass, 2: staged partit
                             const MaskParams &mp, uint32_t P, const uint32_t *num_ptr,
                             uint32_t capacity, uint32_t *status, uint32_t *ticket,
                             const uint32_t *digit_base, int shift, int bits, int idx_bits,
-                            cudaStream_t s, const uint16_t *mask_in = nullptr) {
+                            cudaStream_t s, const uint16_t *mask_in = nullptr,
+                            const uint32_t *hist = nullptr, uint2 *ranges = nullptr,
+                            uint32_t *tile_order = nullptr, int tiles = 0) {
   static unsigned long long seen = 0;
   if (first_use_on_device(seen)) {   // the widest pass (10 bits) needs more than the default 48 KB
     const int big = WARPS * SORT_MAX_BINS * 2 + SORT_MAX_BINS * 4;
@@ -911,10 +965,12 @@ static void launch_one_pass(int last /* 1: unpacking last pass, 2: staged partit
     cudaFuncSetAttribute(sort_last_pass_kernel<ITEMS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          big + SORT_MAX_BINS * 4 + stage_max);
     cudaFuncSetAttribute(sort_last_pass_kernel<ITEMS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         big + SORT_MAX_BINS * 4 + stage_max + SORT_THREADS * ITEMS * 2);
+                         big + SORT_MAX_BINS * 4 + stage_max + SORT_THREADS * ITEMS * 2 +
+                             2 * SORT_MAX_BINS * 4);
   }
   const int nbins = 1 << bits;
-  const int nblk = (int)(((size_t)capacity + SORT_THREADS * ITEMS - 1) / (SORT_THREADS * ITEMS));
+  int nblk = (int)(((size_t)capacity + SORT_THREADS * ITEMS - 1) / (SORT_THREADS * ITEMS));
+  if (last == 2 && nblk < 1) nblk = 1;   // the partition pass also writes the tile ranges
   const size_t smem = (size_t)WARPS * nbins * 2 + (size_t)nbins * 4;
   const size_t stage = (size_t)SORT_THREADS * ITEMS * 8 > (size_t)WARPS * nbins * 4
                            ? (size_t)SORT_THREADS * ITEMS * 8 : (size_t)WARPS * nbins * 4;
@@ -922,13 +978,14 @@ static void launch_one_pass(int last /* 1: unpacking last pass, 2: staged partit
   if (last == 1)
     sort_last_pass_kernel<ITEMS, true><<<nblk, SORT_THREADS, smem + (size_t)nbins * 4 + stage, LS(s)>>>(
         src, keys_out, plist_out, mp, P, num_ptr, capacity, status, ticket, digit_base, shift, bits,
-        idx_bits, nullptr);
+        idx_bits, nullptr, nullptr, nullptr, nullptr, 0);
   else if (last == 2)
     sort_last_pass_kernel<ITEMS, false><<<nblk, SORT_THREADS,
-                                          smem + (size_t)nbins * 4 + stage + (size_t)SORT_THREADS * ITEMS * 2,
+                                          smem + (size_t)nbins * 4 + stage +
+                                              (size_t)SORT_THREADS * ITEMS * 2 + (size_t)nbins * 8,
                                           LS(s)>>>(
         src, dst, nullptr, mp, P, num_ptr, capacity, status, ticket, digit_base, shift, bits,
-        idx_bits, mask_in);
+        idx_bits, mask_in, hist, ranges, tile_order, tiles);
   else
     sort_pass_kernel<ITEMS><<<nblk, SORT_THREADS, smem + (size_t)WARPS * nbins * 4, LS(s)>>>(src, dst, num_ptr, capacity, status,
                                                              ticket, digit_base, shift, bits);
@@ -1008,8 +1065,9 @@ void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, con
   mp.tiles_x = im.tiles_x;
   mp.H = p.H;
   const int single = (sp.npass == 4) ? 3 : -1;
-  launch_digit_scan(b.hist, b.digit_base, sp.npass, im.ranges, im.tile_order, im.tiles, single,
-                    HIST_REPL, s);
+  if (!sort_tile_first(sp, im.tiles))
+    launch_digit_scan(b.hist, b.digit_base, sp.npass, im.ranges, im.tile_order, im.tiles, single,
+                      HIST_REPL, s);
   if (sort_tile_first(sp, im.tiles)) {
     static unsigned long long seen = 0;
     if (first_use_on_device(seen))
@@ -1020,7 +1078,8 @@ void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, con
   launch_one_pass<I>(2, b.words_a, b.words_b, nullptr, nullptr, none, (uint32_t)p.P,             \
                      &g.hdr->num_rendered, capacity, b.status + b.status_off[single],            \
                      b.tickets + single, b.digit_base + single * SORT_MAX_BINS, sp.shift[single], \
-                     sp.bits[single], sp.idx_bits, s, reinterpret_cast<const uint16_t *>(b.keys))
+                     sp.bits[single], sp.idx_bits, s, reinterpret_cast<const uint16_t *>(b.keys), \
+                     b.hist + single * SORT_MAX_BINS, im.ranges, im.tile_order, im.tiles)
     if (items == 16) PART_PASS(16);
     else if (items == 12) PART_PASS(12);
     else PART_PASS(8);
