@@ -27,7 +27,13 @@
 #define SPLAT_DEPTH_BITS 27       // bits(120.0f) - bits(0.1f) < 2^27
 #define SPLAT_ALPHA_MIN 0x3B808081u   // smallest float that is >= 1/255
 
-#define SPLAT_BLOCKS_PER_TILE 8    // 8x4-pixel blocks of a 16x16 tile (compositing work units)
+// The compositing kernels' unit of work ("block"): SPLAT_UNIT_SUBS 4x4 sub-tiles side by side -
+// 2: 8x4 pixels, 8 blocks per tile, every lane of the warp a pixel; 1: 4x4 pixels, 16 blocks per
+// tile, twice the warps with the upper 16 lanes free of pixels (they work in the pair stages)
+#ifndef SPLAT_UNIT_SUBS
+#define SPLAT_UNIT_SUBS 2
+#endif
+#define SPLAT_BLOCKS_PER_TILE (16 / SPLAT_UNIT_SUBS)
 #define SPLAT_MAX_ORDERED_TILES 8192   // the O(tiles^2) work ordering is skipped beyond this
 
 #define PRE_CHUNK 256             // surfels per preprocess block (one thread each)

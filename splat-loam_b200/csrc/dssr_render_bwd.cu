@@ -53,7 +53,7 @@ namespace {
 
 constexpr int SUB = 4;                                            // 4x4 pixels per sub-tile
 constexpr int SUBS_PER_TILE = (SPLAT_TILE / SUB) * (SPLAT_TILE / SUB);   // 16
-constexpr int UNITS_PER_TILE = SUBS_PER_TILE / 2;                 // a warp = two sub-tiles
+constexpr int UNITS_PER_TILE = SPLAT_BLOCKS_PER_TILE;             // a warp = SPLAT_UNIT_SUBS sub-tiles
 #ifndef COMPOSITE_ENT_CAP
 #define COMPOSITE_ENT_CAP 64
 #endif
@@ -126,7 +126,7 @@ struct __align__(16) WarpStage {
 };
 
 // One WARP per CTA = one 8x4 pixel block; CTAs in order of decreasing number of pairs.
-__global__ void __launch_bounds__(32, 14)
+__global__ void __launch_bounds__(32, SPLAT_UNIT_SUBS == 2 ? 14 : 24)
 render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restrict__ bwd_order,
                        const uint32_t *__restrict__ blk_top, const char *__restrict__ bin_base,
                        const BinHeader *__restrict__ bhdr, const float4 *__restrict__ rec,
@@ -145,12 +145,12 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
 #endif
   const uint32_t unit = bwd_order[blockIdx.x];
   const uint32_t tile = unit / UNITS_PER_TILE;
-  const int sub_a = 2 * (int)(unit % UNITS_PER_TILE);           // left sub-tile; right = sub_a + 1
+  const int sub_a = SPLAT_UNIT_SUBS * (int)(unit % UNITS_PER_TILE);           // left sub-tile; right = sub_a + 1
   const int x0 = (tile % tiles_x) * SPLAT_TILE + (sub_a & 3) * SUB;
   const int y0 = (tile / tiles_x) * SPLAT_TILE + (sub_a >> 2) * SUB;
   if (x0 >= W || y0 >= H) return;
   const int px = x0 + SUB * half + (p16 & 3), py = y0 + (p16 >> 2);
-  const bool inside = px < W && py < H;
+  const bool inside = half < SPLAT_UNIT_SUBS && px < W && py < H;
   const size_t HW = (size_t)W * H;
   const size_t pix = (size_t)py * W + px;
 

@@ -50,7 +50,7 @@ namespace {
 
 constexpr int SUB = 4;                                            // 4x4 pixels per sub-tile
 constexpr int SUBS_PER_TILE = (SPLAT_TILE / SUB) * (SPLAT_TILE / SUB);   // 16
-constexpr int UNITS_PER_TILE = SUBS_PER_TILE / 2;                 // a warp = two sub-tiles
+constexpr int UNITS_PER_TILE = SPLAT_BLOCKS_PER_TILE;             // a warp = SPLAT_UNIT_SUBS sub-tiles
 #ifndef COMPOSITE_ENT_CAP
 #define COMPOSITE_ENT_CAP 64
 #endif
@@ -115,7 +115,7 @@ struct __align__(16) FwdStage {
 // One WARP per CTA = one 8x4 pixel block.  CTAs are numbered in order of decreasing tile list
 // length (tile_order), so the hardware's round-robin placement hands every SM a balanced mix
 // of long and short lists.
-__global__ void __launch_bounds__(32, 16)
+__global__ void __launch_bounds__(32, SPLAT_UNIT_SUBS == 2 ? 16 : 24)
 render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restrict__ tile_order,
                       const uint2 *__restrict__ blist, const uint32_t *__restrict__ blk_len,
                       const float4 *__restrict__ rec,
@@ -136,7 +136,7 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
 #endif
   const uint32_t tile = tile_order ? tile_order[work / UNITS_PER_TILE] : work / UNITS_PER_TILE;
   const int unit = work % UNITS_PER_TILE;
-  const int sub_a = 2 * unit;                                   // left sub-tile; right = sub_a + 1
+  const int sub_a = SPLAT_UNIT_SUBS * unit;                                   // left sub-tile; right = sub_a + 1
   const int x0 = (tile % tiles_x) * SPLAT_TILE + (sub_a & 3) * SUB;
   const int y0 = (tile / tiles_x) * SPLAT_TILE + (sub_a >> 2) * SUB;
   if (x0 >= W || y0 >= H) {
@@ -144,7 +144,7 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
     return;
   }
   const int px = x0 + SUB * half + (p16 & 3), py = y0 + (p16 >> 2);
-  const bool inside = px < W && py < H;
+  const bool inside = half < SPLAT_UNIT_SUBS && px < W && py < H;
   const float fx = projmatrix[0], fy = projmatrix[5], cx = projmatrix[8], cy = projmatrix[9];
   const float pxf = (float)px, pyf = (float)py;
   {
@@ -255,7 +255,7 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
           if (!(yf < cb.z) && !(yf > cb.w)) rows |= 1u << r;
         }
 #pragma unroll
-        for (int q = 0; q < 2 * SUB; q++) {
+        for (int q = 0; q < SPLAT_UNIT_SUBS * SUB; q++) {
           const float xf = (float)(x0 + q);
           if ((!(xf < cb.x) && !(xf > cb.y)) || !(xf < cb.x + period)) cols |= 1u << q;
         }
@@ -474,7 +474,7 @@ bwd_order_kernel(const uint32_t *__restrict__ sub_cost, int units, uint32_t *__r
 
 void launch_bwd_order(const ImageView &im, const FillList &fill, cudaStream_t s) {
   bwd_order_kernel<<<1 + 2 * splat_sm_count(), 1024, 0, LS(s)>>>(
-      im.sub_cost, im.tiles * SUBS_PER_TILE / 2, im.bwd_order, fill);
+      im.sub_cost, im.tiles * UNITS_PER_TILE, im.bwd_order, fill);
 }
 
 void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageView &im,

@@ -791,7 +791,7 @@ tile_sort_kernel(unsigned long long *words, unsigned long long *alt,
   for (uint32_t i = e0; i < e1; i++) {
     const uint32_t m = (uint32_t)(fin[i] >> 48);
 #pragma unroll
-    for (int u = 0; u < SPLAT_BLOCKS_PER_TILE; u++) bcnt[u] += ((m >> (2 * u)) & 3u) != 0u;
+    for (int u = 0; u < SPLAT_BLOCKS_PER_TILE; u++) bcnt[u] += ((m >> (SPLAT_UNIT_SUBS * u)) & ((1u << SPLAT_UNIT_SUBS) - 1u)) != 0u;
   }
 #pragma unroll
   for (int u = 0; u < SPLAT_BLOCKS_PER_TILE; u++) {
@@ -826,7 +826,7 @@ tile_sort_kernel(unsigned long long *words, unsigned long long *alt,
     const uint2 e = make_uint2((uint32_t)(k & idx_mask), i);
 #pragma unroll
     for (int u = 0; u < SPLAT_BLOCKS_PER_TILE; u++)
-      if (((m >> (2 * u)) & 3u) != 0u) bbase[(size_t)u * n + bcnt[u]++] = e;
+      if (((m >> (SPLAT_UNIT_SUBS * u)) & ((1u << SPLAT_UNIT_SUBS) - 1u)) != 0u) bbase[(size_t)u * n + bcnt[u]++] = e;
   }
   TRACE(11)
 }
@@ -871,7 +871,7 @@ block_list_kernel(const uint2 *__restrict__ ranges, uint32_t capacity,
     const uint32_t m = i < w1 ? (uint32_t)sm[i] : 0u;
 #pragma unroll
     for (int u = 0; u < SPLAT_BLOCKS_PER_TILE; u++)
-      cnt[u] += __popc(__ballot_sync(0xffffffffu, ((m >> (2 * u)) & 3u) != 0u));
+      cnt[u] += __popc(__ballot_sync(0xffffffffu, ((m >> (SPLAT_UNIT_SUBS * u)) & ((1u << SPLAT_UNIT_SUBS) - 1u)) != 0u));
   }
   if (lane == 0) {
 #pragma unroll
@@ -901,7 +901,7 @@ block_list_kernel(const uint2 *__restrict__ ranges, uint32_t capacity,
     const uint32_t id = in ? pl[i] : 0u;
 #pragma unroll
     for (int u = 0; u < SPLAT_BLOCKS_PER_TILE; u++) {
-      const bool hit = ((m >> (2 * u)) & 3u) != 0u;
+      const bool hit = ((m >> (SPLAT_UNIT_SUBS * u)) & ((1u << SPLAT_UNIT_SUBS) - 1u)) != 0u;
       const uint32_t vote = __ballot_sync(0xffffffffu, hit);
       if (hit) base[(size_t)u * n + off[u] + __popc(vote & lt)] = make_uint2(id, i);
       off[u] += __popc(vote);
