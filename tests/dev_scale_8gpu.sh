@@ -1,5 +1,6 @@
 #!/bin/bash
 # scaling runs on an 8-GPU box: N = 8, 4, 2, 1 of our arm, the reference arm and the NCCL variant at 8
+mkdir -p gpurun_out
 python -m pytest tests/test_gpu_exchange_mp.py tests/test_gpu_abi_more.py -m gpu -q 2>&1 | tail -2
 for n in 8 4 2; do
   python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2951$n bench.py --gpus $n --steps 100 > gpurun_out/r2_scale$n.json 2> gpurun_out/r2_scale$n.err
