@@ -197,8 +197,9 @@ def pipelined_e2e(dev, steps, flush, copy_in, frame_fn, out_specs):
     and, for a sharded upload, the all-gather that completes them), runs `frame_fn(b)` -> list
     of device result tensors, and copies the results back to pinned host memory, all inside
     the timed region.  Inputs, results and host buffers are double-buffered so the copies of
-    neighbouring steps overlap the compute (copy engines on side streams); the L2 flush is
-    also inside the timed region.  Returns (ms per step, D2H bytes per step)."""
+    neighbouring steps overlap the compute (copy engines on side streams; step i + 1's upload
+    is enqueued ahead of step i's frame); the L2 flush is also inside the timed region.
+    Returns (ms per step, D2H bytes per step)."""
     main = torch.cuda.current_stream(dev)
     s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
     h_out = [[torch.empty(sh, dtype=torch.float32).pin_memory() for sh in out_specs] for _ in range(2)]
@@ -207,14 +208,23 @@ def pipelined_e2e(dev, steps, flush, copy_in, frame_fn, out_specs):
     ev_res = [torch.cuda.Event() for _ in range(2)]
     ev_out = [torch.cuda.Event() for _ in range(2)]
 
+    def upload(i):
+        b = i & 1
+        with torch.cuda.stream(s_in):
+            if i >= 2:
+                s_in.wait_event(ev_used[b])        # the frame two steps ago has read them
+            copy_in(b)
+            ev_in[b].record(s_in)
+
     def run(n):
+        # The upload of step i + 1 is enqueued BEFORE the frame of step i: a frame's forward
+        # blocks the host until its instance count has landed (both arms do), and an upload
+        # enqueued after that wait would start late and leave the GPU idle at the next step.
+        upload(0)
         for i in range(n):
             b = i & 1
-            with torch.cuda.stream(s_in):
-                if i >= 2:
-                    s_in.wait_event(ev_used[b])        # the frame two steps ago has read them
-                copy_in(b)
-                ev_in[b].record(s_in)
+            if i + 1 < n:
+                upload(i + 1)
             main.wait_event(ev_in[b])
             if i >= 2:
                 main.wait_event(ev_out[b])             # result slot b has been drained
