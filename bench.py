@@ -191,14 +191,16 @@ def consumed_instances(nc, ranges, H, W):
     return int(pad.reshape(gy, 16, gx, 16).max(axis=(1, 3)).sum())
 
 
-def pipelined_e2e(dev, steps, flush, copy_in, frame_fn, out_specs):
+def pipelined_e2e(dev, steps, flush, copy_in, frame_fn, out_specs, prefetch=True):
     """End-to-end protocol shared by both arms: every step brings that step's inputs from
     pinned host memory into device slot b (`copy_in(b)`, enqueued on a side stream: H2D copies
     and, for a sharded upload, the all-gather that completes them), runs `frame_fn(b)` -> list
     of device result tensors, and copies the results back to pinned host memory, all inside
     the timed region.  Inputs, results and host buffers are double-buffered so the copies of
-    neighbouring steps overlap the compute (copy engines on side streams; step i + 1's upload
-    is enqueued ahead of step i's frame); the L2 flush is also inside the timed region.
+    neighbouring steps overlap the compute (copy engines on side streams); the L2 flush is also
+    inside the timed region.  `prefetch`: step i + 1's upload is enqueued ahead of step i's
+    frame (plain copies); without it, after the frame (an upload that ends in a collective:
+    measured on 8 GPUs, the all-gather enqueued early costs more than its late start).
     Returns (ms per step, D2H bytes per step)."""
     main = torch.cuda.current_stream(dev)
     s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
@@ -220,11 +222,14 @@ def pipelined_e2e(dev, steps, flush, copy_in, frame_fn, out_specs):
         # The upload of step i + 1 is enqueued BEFORE the frame of step i: a frame's forward
         # blocks the host until its instance count has landed (both arms do), and an upload
         # enqueued after that wait would start late and leave the GPU idle at the next step.
-        upload(0)
+        if prefetch:
+            upload(0)
         for i in range(n):
             b = i & 1
-            if i + 1 < n:
+            if prefetch and i + 1 < n:
                 upload(i + 1)
+            elif not prefetch:
+                upload(i)
             main.wait_event(ev_in[b])
             if i >= 2:
                 main.wait_event(ev_out[b])             # result slot b has been drained
@@ -422,7 +427,7 @@ def run_ours(args, rank, world, local_rank):
 
     barrier()
     e2e_ms_step, d2h = pipelined_e2e(dev, args.steps, flush, copy_in, e2e_frame,
-                                     [(7, H, W), (hi - lo, 10)])
+                                     [(7, H, W), (hi - lo, 10)], prefetch=not shard)
     barrier()
     if xchg:
         xchg.check()
