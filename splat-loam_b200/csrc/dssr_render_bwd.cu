@@ -52,7 +52,6 @@ __device__ __forceinline__ unsigned long long btime() {
 namespace {
 
 constexpr int SUB = 4;                                            // 4x4 pixels per sub-tile
-constexpr int SUBS_PER_TILE = (SPLAT_TILE / SUB) * (SPLAT_TILE / SUB);   // 16
 constexpr int UNITS_PER_TILE = SPLAT_BLOCKS_PER_TILE;             // a warp = SPLAT_UNIT_SUBS sub-tiles
 #ifndef COMPOSITE_ENT_CAP
 #define COMPOSITE_ENT_CAP 64
@@ -205,7 +204,6 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
   st.gN[0][lane] = pc.gN0; st.gN[1][lane] = pc.gN1; st.gN[2][lane] = pc.gN2;
 
   int chunk = (int)top - 1;
-  const uint32_t lt = (1u << lane) - 1u;
   // Software pipeline of the walk (back to front): the step words are fetched four steps
   // ahead of their use, the blended entries' list entries and pixel masks three steps ahead,
   // their records one step ahead (into registers) - every load's address comes from a load

@@ -49,7 +49,6 @@ __device__ __forceinline__ unsigned long long rtime() {
 namespace {
 
 constexpr int SUB = 4;                                            // 4x4 pixels per sub-tile
-constexpr int SUBS_PER_TILE = (SPLAT_TILE / SUB) * (SPLAT_TILE / SUB);   // 16
 constexpr int UNITS_PER_TILE = SPLAT_BLOCKS_PER_TILE;             // a warp = SPLAT_UNIT_SUBS sub-tiles
 #ifndef COMPOSITE_ENT_CAP
 #define COMPOSITE_ENT_CAP 64
@@ -170,7 +169,6 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
   const uint2 *bl = blist + ubase;
   uint32_t *bw = bwords + (ubase >> 5) + tile * UNITS_PER_TILE + unit;
   uint32_t *bp = bpix + ubase;
-  const uint32_t lt = (1u << lane) - 1u;
 
   PixelState ps;
   ps.T = 1.0f;

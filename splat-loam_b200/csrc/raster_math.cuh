@@ -63,14 +63,6 @@ struct Hit {
   float depth, G, alpha;
 };
 
-// Conservative cutoff on rho = min(rho3d, rho2d): beyond it alpha = min(0.99, opa *
-// exp(-rho/2)) is below 1/255 with a 0.4 % margin (far above any rounding of the exact
-// evaluation).  Same formula as the cull box of the preprocess kernel.
-__device__ __forceinline__ float rho_cutoff(float opa) {
-  // __logf: absolute error < 2^-21, three orders of magnitude inside the margin
-  return 2.0f * __logf(255.0f * opa) * 1.002f + 0.01f;
-}
-
 // First half of the evaluation: the transformed planes, their cross product and the
 // pixel-space distance (forward.cu:265-277).  Returns false when this lane provably ends in
 // one of the reference's `continue`s: p.z == 0, or both rho3d = |p.xy|^2 / p.z^2 and rho2d
