@@ -11,3 +11,4 @@ ncu --set full --clock-control none --import-source on --launch-skip 20 -o gpuru
     python tests/dev_profile.py C2 3 > gpurun_out/prof_ncu.log 2>&1
 tail -1 gpurun_out/bench_ours.json | cut -c1-600
 tail -1 gpurun_out/bench_ref.json | cut -c1-300
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -1
