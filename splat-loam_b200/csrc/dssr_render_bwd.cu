@@ -422,13 +422,13 @@ render_backward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restr
         if (valid && (lane == 0 || jp != j)) {
           const size_t gid = st.ent_id[j];
           float *tm = dL_dtransMat + gid * 12, *nr = dL_dnormal + gid * 3;
+          // (unconditional: the sums are zero only in the first six of a 2D-filter entry, and
+          // thirteen compare-and-branch pairs cost more than those few atomics)
 #pragma unroll
-          for (int i = 0; i < 9; i++)
-            if (v[i] != 0.0f) atomicAdd(tm + (i / 3) * 4 + (i % 3), v[i]);
+          for (int i = 0; i < 9; i++) atomicAdd(tm + (i / 3) * 4 + (i % 3), v[i]);
 #pragma unroll
-          for (int i = 0; i < 3; i++)
-            if (v[9 + i] != 0.0f) atomicAdd(nr + i, v[9 + i]);
-          if (v[12] != 0.0f) atomicAdd(dL_dopacity + gid, v[12]);
+          for (int i = 0; i < 3; i++) atomicAdd(nr + i, v[9 + i]);
+          atomicAdd(dL_dopacity + gid, v[12]);
         }
       }
       __syncwarp();

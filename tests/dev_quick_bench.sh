@@ -1,5 +1,5 @@
 mkdir -p gpurun_out
-python -m pytest tests/test_gpu_raster.py tests/test_gpu_raster_more.py tests/test_gpu_abi_more.py -x -q 2>&1 | tail -6
+python -m pytest tests/test_gpu_raster.py tests/test_gpu_raster_more.py tests/test_gpu_abi_more.py -x -q 2>&1 | tail -3
 python bench.py --steps 30 --warmup 5 2>/dev/null | tail -1 > gpurun_out/quick.json
 python - <<PY
 import json
