@@ -219,7 +219,9 @@ typedef struct {
 SPLAT_API int splat_activation_adam_step(const splat_adam_args *args);
 
 /* Buffer sizes the callbacks will be asked for (mirrors required<T>(),
- * DSSR/cuda_rasterizer/rasterizer_impl.h:59-64). */
+ * DSSR/cuda_rasterizer/rasterizer_impl.h:59-64).  The binning buffer takes 126 bytes of
+ * address space per instance of capacity (the reference: 28); most of it is the worst-case
+ * room of the per-block lists, of which a frame touches about a fifth. */
 SPLAT_API size_t dssr_geometry_bytes(int P);
 SPLAT_API size_t dssr_image_bytes(int W, int H);
 SPLAT_API size_t dssr_binning_bytes(int64_t capacity, int W, int H, int P, int keep_unsorted);
@@ -233,7 +235,10 @@ SPLAT_API size_t dssr_binning_bytes(int64_t capacity, int W, int H, int P, int k
  * The reference has no such call; its tests re-derive the same arrays with
  * GeometryState/BinningState/ImageState::fromChunk (rasterizer_impl.h:18-56).
  * "transMat" and "normal_opacity" are materialised into `scratch` (device, at least
- * 16*P floats) because the product stores them in a packed record. */
+ * 16*P floats) because the product stores them in a packed record.  "keys" are
+ * materialised on request too when the tile-first sort produced the frame (images of
+ * up to 1024 tiles and 2 M surfels): that sort never writes point_list_keys, every key
+ * is (tile << 32) | bits(depths[point_list[i]]) and is rebuilt from those arrays. */
 SPLAT_API int dssr_debug_state(const char *geom_buffer, const char *binning_buffer,
                      const char *image_buffer, const char *name, float *scratch,
                      void **ptr, size_t *count, void *stream);
