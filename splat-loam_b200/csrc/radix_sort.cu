@@ -929,6 +929,13 @@ void launch_digit_scan(const uint32_t *hist, uint32_t *digit_base, int npass, ui
 // keys per thread are two waves, the second a third full; 287 CTAs of 12 are two full, shorter
 // ones.  `n_estimate`: the expected number of words (the capacity may be a generous hint).
 static int pick_items(uint32_t n_estimate) {
+  // SPLAT_B200_SORT_ITEMS=8|12|16 overrides the choice (developer A/B switch)
+  static const int forced = [] {
+    const char *e = getenv("SPLAT_B200_SORT_ITEMS");
+    const int v = e ? atoi(e) : 0;
+    return (v == 8 || v == 12 || v == 16) ? v : 0;
+  }();
+  if (forced) return forced;
   const int sms = splat_sm_count();
   const int choices[3] = {16, 12, 8};
   int best = 16;
