@@ -75,13 +75,16 @@ def test_gradient_outputs_anywhere_in_memory(native_lib, layout):
     assert np.all(host[~used] == 12345.0)          # nothing outside the seven arrays was touched
 
 
-def test_small_hint_with_two_tile_passes_on_poisoned_buffers(native_lib):
-    """More than 1024 tiles (tile ranges come from identify_ranges_kernel) with a capacity hint
-    far below the instance count, the buffers the allocator hands out pre-filled with 0xFF: the
-    hinted attempt must stay inside its arrays and the exact-size re-run give the usual
-    result."""
+@pytest.mark.parametrize("dims", [(144, 2064, 45.0, 60000), (64, 1024, 33.2, 60000)],
+                         ids=["global_sort_two_tile_passes", "tile_first_sort"])
+def test_small_hint_with_two_tile_passes_on_poisoned_buffers(native_lib, dims):
+    """A capacity hint far below the instance count, the buffers the allocator hands out
+    pre-filled with 0xFF: the hinted attempt must stay inside its arrays and the exact-size
+    re-run give the usual result.  With more than 1024 tiles the tile ranges come from
+    identify_ranges_kernel (global sort path); with fewer, from the tile histogram, and the
+    per-tile sort and the block lists run over ranges with holes of stale bytes."""
     from diff_surfel_spherical_rasterization import _C
-    s = scenes.make_scene((144, 2064, 45.0, 60000))
+    s = scenes.make_scene(dims)
     c = to_cuda(s)
     _C._hints.clear()
     ref = _forward(c, s)                       # exact-size path
