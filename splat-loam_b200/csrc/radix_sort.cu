@@ -1,6 +1,5 @@
-// radix_sort.cu — hand-written stable LSD radix sort of the instance words, one
-// kernel per digit ("onesweep": chained scan with decoupled look-back), plus the
-// digit-base scan that also yields the per-tile ranges.
+// radix_sort.cu — the sort of the instance words and what is derived from it: the per-tile
+// ranges, point_list and the per-block lists the compositing kernels walk.
 //
 // Replaces (submodules/diff-surfel-spherical-rasterization/cuda_rasterizer/):
 //   cub::DeviceRadixSort::SortPairs(keys u64, values u32, N, 0, 32+bit)
@@ -12,11 +11,16 @@
 // surfel idx, so "stable by emission order" == "ties broken by idx" (a surfel that
 // emits the same tile twice emits identical pairs).  We therefore sort ONE 64-bit word
 //   [ tile | depth_bits - bits(0.1f) : 27 | idx ]
-// stably on its [tile|depth27] bits only: 3 passes x 9 bits for the depth (visible
-// depths lie in (0.1, 120] so 27 bits cover them) and one pass of <= 10 bits for the
-// tile (two when there are more than 1024 tiles) — 4 passes of 8 B/instance instead
-// of CUB's 6 passes of 12 B/instance.  The last pass unpacks to the reference's
-// point_list_keys (u64) and point_list (u32), which are therefore bit-identical.
+// stably on its [tile|depth27] bits only (visible depths lie in (0.1, 120], so 27 bits cover
+// them).  Two paths, same result - the reference's point_list / point_list_keys, bit for bit:
+//   * tile-first (<= 1024 tiles, <= 2 M surfels; second half of this file): one stable
+//     partition of the words by tile (the tile histogram comes from the emit kernel), then
+//     one CTA per tile sorts the tile's range on the 27 depth bits in shared memory;
+//   * global (anything else): stable LSD radix sort, one kernel per digit ("onesweep":
+//     chained scan with decoupled look-back) - 3 passes x 9 bits for the depth and one or two
+//     passes for the tile, 8 B/instance each instead of CUB's 6 passes of 12 B/instance -
+//     after a digit-base scan that also yields the per-tile ranges.
+// The pass kernels also serve simple-knn's Morton sort (sknn.cu).
 #include <cstdlib>
 #include <cstring>
 
