@@ -12,17 +12,19 @@
 // entry), and those are exactly the pairs the reference's backward ends up processing
 // (backward.cu:132 skips entries past a pixel's last contributor, :152-182 repeat the
 // forward's tests on the same floats).  So the backward tests nothing:
-//   * a warp owns an 8x4 pixel block (two 4x4 sub-tiles) and walks its tile's list back to
-//     front; per 32-entry step it reads the two step words, and only the blended entries'
-//     records (64 B, L2-resident) and pixel masks;
+//   * a warp owns an 8x4 pixel block (two 4x4 sub-tiles) and walks the BLOCK's list (the
+//     tile's entries that can touch it, radix_sort.cu) back to front, as far as the forward
+//     got; per 32-entry step it reads the step word, and only the blended entries' list
+//     entries (surfel index, list position), records (64 B, L2-resident) and pixel masks;
 //   * the blended (pixel, entry) pairs are laid end to end and processed 32 at a time, ONE PAIR
 //     PER LANE whatever its pixel and entry (P1: intersection, alpha, depth);
 //   * the per-pixel recurrences (backward.cu:183-237: T, the accum_* terms, last_dL_dT), the
 //     only sequential part, run on the pixel's own lane over that pixel's pairs of the batch,
 //     in list order, from shared memory (P2);
 //   * back on the pair lanes the gradient of the pair w.r.t. the surfel's 13 values is
-//     finished (P3), the batch's contributions are summed per entry through shared memory and
-//     one atomic per (entry, component) goes out.
+//     finished (P3), the batch's contributions are summed per entry by a segmented shuffle
+//     reduction (an entry's pairs sit in consecutive lanes) and one atomic per (entry,
+//     component) goes out.
 // The reference's backward is not the adjoint of its forward (SURVEY.md §8 a10, quirks Q1-Q4,
 // Q7); it is reproduced as written.
 #include "peer_exchange.cuh"

@@ -548,8 +548,10 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
 // stable partition pass (sort_last_pass_kernel<.., false>) and each tile's range - a few
 // thousand words - is then sorted on its 27 depth bits by one CTA in shared memory: three
 // 9-bit LSD passes that never leave the SM, instead of three passes over all instances through
-// L2 with a chained scan each.  The write-out unpacks to the reference's point_list_keys /
-// point_list and computes the sub-tile masks, as the last global pass did.
+// L2 with a chained scan each.  The write-out produces the reference's point_list and the
+// tile's 8 block lists; the sub-tile masks it needs ride in the words' top 16 bits (computed by
+// the emit kernel, packed by the partition pass: the tile bits are redundant once a word lies
+// in its tile's range).  point_list_keys is not written (rebuild_keys_kernel).
 // Ranges longer than TS_CAP words are sorted by the same CTA with the same passes in global
 // memory (the tile's range of the two word arrays as ping and pong).
 constexpr int TS_THREADS = 1024;
