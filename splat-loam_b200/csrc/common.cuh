@@ -12,9 +12,11 @@
 //        f4[2] = Tw.z n.x  n.y  n.z      f4[3] = opacity cx cy |Tw|
 //    cull (16 B / surfel): conservative pixel-space box {xmin,xmax,ymin,ymax} outside
 //        of which the surfel provably fails the alpha >= 1/255 test.
-//  image buffer     [final_T f32[3HW] (T, M1, M2) | n_contrib u32[2HW] | ranges uint2[tiles]]
+//  image buffer     [final_T f32[3HW] (T, M1, M2) | n_contrib u32[2HW] | ranges uint2[tiles] |
+//                    tile_order | sub_cost | bwd_order | blk_len | blk_top]  (ImageLayout)
 //  binning buffer   [BinHeader | point_list u32[C] | keys u64[C] | words_a u64[C] |
-//                    words_b u64[C] | (keys_unsorted u64[C]) | sort tables]
+//                    words_b u64[C] | sub_mask u16[C] | blist uint2[8C] | bpix u32[8C] |
+//                    bwords | (keys_unsorted u64[C]) | sort tables]          (BinLayout)
 #pragma once
 #include <cstdint>
 #include <cstdio>

@@ -6,7 +6,7 @@
 // The reference runs one 256-thread CTA per 16x16 tile; every pixel walks the tile's whole
 // depth-sorted list, evaluates every entry and the CTA leaves only when all 256 pixels are
 // done.  Here the unit of work is a WARP that owns an 8x4 pixel block (two 4x4 sub-tiles) and
-// walks its tile's list on its own, in three stages that each keep the 32 lanes busy:
+// works through its own list of the tile's entries, in three stages that each keep the 32 lanes busy:
 //   * gather: 32 entries of the BLOCK's list per step (block_list_kernel, radix_sort.cu: the
 //     tile's entries whose 16-bit sub-tile mask touches the block, a few per cent of the tile's
 //     list); they are staged in shared memory - 64-byte record and 16-byte cull box, 128-bit
