@@ -351,6 +351,40 @@ void splat_count_launch(int n = 1);
 // LS(stream): the stream argument of a <<<>>> launch, counting the launch on the way
 #define LS(s) (splat_count_launch(1), (s))
 
+// Programmatic dependent launch (sm_90+): consecutive kernels of a frame are launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, so that a kernel's CTAs are scheduled while
+// the previous kernel's last CTAs still run (its launch latency and prologue hide under that
+// tail).  Every such kernel starts with grid_dependency_wait() - nothing the previous kernel
+// wrote is touched before it has completed and flushed - and lets its own successor go at once
+// with grid_launch_dependents() (the successor is only scheduled once all CTAs of this kernel
+// have started, and waits at its own top).  Both are no-ops in a kernel launched the plain way.
+// SPLAT_B200_PDL=0 launches everything the plain way (developer A/B switch).
+#ifdef __CUDACC__
+__device__ __forceinline__ void grid_dependency_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+__device__ __forceinline__ void grid_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+bool splat_pdl_enabled();
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                     cudaStream_t s, Args &&...args) {
+  splat_count_launch(1);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = splat_pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
 // Function attributes (opt-in shared memory, carve-out) are per device: true the first time a
 // call site runs on the current device (one bit per device in the caller's static mask).
 static inline bool first_use_on_device(unsigned long long &seen) {

@@ -167,6 +167,14 @@ int run_binning_and_render(const dssr_forward_args *a, const FwdParams &fp,
 
 void splat_count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
+bool splat_pdl_enabled() {
+  static const bool on = [] {
+    const char *e = getenv("SPLAT_B200_PDL");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
 int splat_sm_count() {
   static std::atomic<int> cache[MAX_DEVICES];
   int dev = 0;

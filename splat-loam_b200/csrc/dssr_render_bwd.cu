@@ -469,6 +469,7 @@ backward_preprocess_kernel(int P, const int *__restrict__ radii,
                            const float *__restrict__ dL_dopacity, float *dL_dmeans3D,
                            float *dL_dscales, float *dL_drot, float *packed,
                            int packed_accumulate, XchgView xv) {
+  grid_dependency_wait();            // (see launch_pdl, common.cuh)
   static_assert(XCHG_SLICE_ALIGN == 256, "one CTA = one 256-row block with a single owner");
   __shared__ __align__(16) float s_rows[PUSH ? XCHG_SLICE_ALIGN * XCHG_ROW : 4];
   __shared__ float m[16];
@@ -573,19 +574,21 @@ void launch_render_backward(const BwdParams &p, const GeomView &g, const ImageVi
   if (first_use_on_device(seen))   // one-warp CTAs with ~10 KB each: residency needs the carve-out
     cudaFuncSetAttribute(render_backward_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                          cudaSharedmemCarveoutMaxShared);
-  render_backward_kernel<<<im.tiles * UNITS_PER_TILE, 32, 0, LS(s)>>>(
-      im.ranges, im.bwd_order, im.blk_top, reinterpret_cast<const char *>(b.hdr), b.hdr, g.rec,
+  // (launched the plain way: scheduled while the fill blocks of the work-order kernel still run,
+  // its CTAs - numbered by decreasing cost for a round-robin placement on an empty machine -
+  // landed unevenly and the kernel took 189 instead of 170 us)
+  render_backward_kernel<<<im.tiles * UNITS_PER_TILE, 32, 0, LS(s)>>>(im.ranges, im.bwd_order, im.blk_top, reinterpret_cast<const char *>(b.hdr), b.hdr, g.rec,
       p.projmatrix, p.W, p.H, im.tiles_x, (uint32_t)p.P, im.final_T, im.n_contrib, p.dL_dout, p.dL_dtransMat, p.dL_dnormal, p.dL_dopacity);
 }
 
 void launch_backward_preprocess(const BwdParams &p, cudaStream_t s) {
   if (p.push)
-    backward_preprocess_kernel<true><<<(p.P + 255) / 256, 256, 0, LS(s)>>>(
+    launch_pdl(backward_preprocess_kernel<true>, dim3((p.P + 255) / 256), dim3(256), 0, s,
         p.P, p.radii, p.scales, p.rotations, p.viewmatrix, p.dL_dtransMat, p.dL_dnormal,
         p.dL_dopacity, p.dL_dmeans3D, p.dL_dscales, p.dL_drotations, p.packed,
         p.packed_accumulate, *p.push);
   else
-    backward_preprocess_kernel<false><<<(p.P + 255) / 256, 256, 0, LS(s)>>>(
+    launch_pdl(backward_preprocess_kernel<false>, dim3((p.P + 255) / 256), dim3(256), 0, s,
         p.P, p.radii, p.scales, p.rotations, p.viewmatrix, p.dL_dtransMat, p.dL_dnormal,
         p.dL_dopacity, p.dL_dmeans3D, p.dL_dscales, p.dL_drotations, p.packed,
         p.packed_accumulate, XchgView());

@@ -124,6 +124,7 @@ render_forward_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restri
                       float *__restrict__ out, uint32_t *__restrict__ unit_cost,
                       uint32_t *__restrict__ blk_top, uint32_t *__restrict__ bwords,
                       uint32_t *__restrict__ bpix) {
+  grid_dependency_wait();            // (see launch_pdl, common.cuh)
   __shared__ FwdStage st;
   const int lane = threadIdx.x, half = lane >> 4, p16 = lane & 15;
   const uint32_t full = 0xffffffffu;
@@ -482,7 +483,7 @@ void launch_render_forward(const FwdParams &p, const GeomView &g, const ImageVie
   if (first_use_on_device(seen))   // one-warp CTAs: residency is limited by the carve-out
     cudaFuncSetAttribute(render_forward_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                          cudaSharedmemCarveoutMaxShared);
-  render_forward_kernel<<<im.tiles * UNITS_PER_TILE, 32, 0, LS(s)>>>(
+  launch_pdl(render_forward_kernel, dim3(im.tiles * UNITS_PER_TILE), dim3(32), 0, s,
       im.ranges, order, b.blist, im.blk_len, g.rec, g.cull, p.projmatrix, p.W, p.H, im.tiles_x,
       capacity, (uint32_t)p.P, im.final_T, im.n_contrib, p.out_maps, im.sub_cost, im.blk_top,
       b.bwords, b.bpix);

@@ -277,6 +277,8 @@ sort_last_pass_kernel(const unsigned long long *__restrict__ in,
                       const uint32_t *__restrict__ digit_base, int shift, int bits, int idx_bits,
                       const uint16_t *__restrict__ mask_in, const uint32_t *__restrict__ hist,
                       uint2 *ranges, uint32_t *tile_order, int tiles) {
+  grid_dependency_wait();            // (see launch_pdl, common.cuh)
+  grid_launch_dependents();
   extern __shared__ uint32_t smem[];
   const int bins = 1 << bits;
   uint16_t *s_cnt = reinterpret_cast<uint16_t *>(smem);            // [WARPS][bins]
@@ -613,6 +615,8 @@ tile_sort_kernel(unsigned long long *words, unsigned long long *alt,
                  const uint2 *__restrict__ ranges, const uint32_t *__restrict__ tile_order,
                  uint32_t capacity, uint32_t *__restrict__ plist_out, int idx_bits,
                  uint2 *__restrict__ blist, uint32_t *__restrict__ blk_len) {
+  grid_dependency_wait();            // (see launch_pdl, common.cuh)
+  grid_launch_dependents();
   extern __shared__ unsigned long long ts_smem[];
   unsigned long long *s_buf = ts_smem;                                   // [TS_CAP]
   uint32_t *tbl = reinterpret_cast<uint32_t *>(s_buf + TS_CAP);          // [TS_WARPS][TS_BINS]
@@ -993,12 +997,10 @@ static void launch_one_pass(int last /* 1: unpacking last pass, 2: staged partit
         src, keys_out, plist_out, mp, P, num_ptr, capacity, status, ticket, digit_base, shift, bits,
         idx_bits, nullptr, nullptr, nullptr, nullptr, 0);
   else if (last == 2)
-    sort_last_pass_kernel<ITEMS, false><<<nblk, SORT_THREADS,
-                                          smem + (size_t)nbins * 4 + stage +
-                                              (size_t)SORT_THREADS * ITEMS * 2 + (size_t)nbins * 8,
-                                          LS(s)>>>(
-        src, dst, nullptr, mp, P, num_ptr, capacity, status, ticket, digit_base, shift, bits,
-        idx_bits, mask_in, hist, ranges, tile_order, tiles);
+    launch_pdl(sort_last_pass_kernel<ITEMS, false>, dim3(nblk), dim3(SORT_THREADS),
+               smem + (size_t)nbins * 4 + stage + (size_t)SORT_THREADS * ITEMS * 2 + (size_t)nbins * 8,
+               s, src, dst, nullptr, mp, P, num_ptr, capacity, status, ticket, digit_base, shift,
+               bits, idx_bits, mask_in, hist, ranges, tile_order, tiles);
   else
     sort_pass_kernel<ITEMS><<<nblk, SORT_THREADS, smem + (size_t)WARPS * nbins * 4, LS(s)>>>(src, dst, num_ptr, capacity, status,
                                                              ticket, digit_base, shift, bits);
@@ -1097,9 +1099,9 @@ void launch_sort(const FwdParams &p, const GeomView &g, const ImageView &im, con
     else if (items == 12) PART_PASS(12);
     else PART_PASS(8);
 #undef PART_PASS
-    tile_sort_kernel<<<im.tiles, TS_THREADS, TS_SMEM, LS(s)>>>(
-        b.words_b, b.words_a, im.ranges, im.tile_order, capacity, b.point_list, sp.idx_bits,
-        b.blist, im.blk_len);
+    launch_pdl(tile_sort_kernel, dim3(im.tiles), dim3(TS_THREADS), TS_SMEM, s, b.words_b,
+               b.words_a, im.ranges, im.tile_order, capacity, b.point_list, sp.idx_bits, b.blist,
+               im.blk_len);
     return;
   }
   launch_sort_passes(b.words_a, b.words_b, b.keys, b.point_list, &g.hdr->num_rendered,
